@@ -1,0 +1,196 @@
+/*
+ * herdb.h -- C ABI of the B200 gate-evaluation backend for herd-fhe/herdsman.
+ *
+ * This is the drop-in boundary for herdsman's one data-parallel hot path:
+ * "apply a boolean circuit, gate by gate, to every row of an encrypted
+ * data-frame partition".  Every entry point cites the reference interface it
+ * stands behind (paths relative to the herdsman tree):
+ *
+ *   herdb_map_async        == IWorkerGroup::schedule_task(MapTask)
+ *                             include/execution/worker/i_worker_group.hpp:44-48,
+ *                             common/include/herd/common/model/worker/task.hpp:12-21,
+ *                             wire form proto/src/worker.proto:28-37,57-61
+ *   herdb_done_fn/status   == IWorkerGroup::TaskHandle::Status + completion callback
+ *                             include/execution/worker/i_worker_group.hpp:15-42,
+ *                             src/execution/worker/i_worker_group.cpp:4-20
+ *   herdb_circuit/node/edge== herd::common::Circuit / node_t / DAG edges
+ *                             common/include/herd/common/model/circuit/circuit.hpp:14-30,
+ *                             nodes.hpp:12-43, operation.hpp:12-20, dag.hpp (parents() order
+ *                             = edge insertion order, dag.hpp:208-230)
+ *   herdb_load_key         == <key_dir>/<session>/<int(SchemaType)>.key
+ *                             src/service/key_service.cpp:19-44
+ *   partition files        == <storage_dir>/<session>/<data_frame>/<partition>, rows framed
+ *                             [u32 len][payload]  src/service/storage_service.cpp:19-28,99-150
+ *   gate arithmetic        == OpenFHE binfhe v1.0.x EvalBinGate/EvalNOT (not in the reference
+ *                             tree; restated in oracle/oracle.c)
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every function
+ * returns 0 or a negative herdb_status code and never throws; herdb_strerror()
+ * names a code, herdb_last_error() gives the detailed message of the last
+ * failure on that context.  There is NO CPU fallback: without a CUDA device
+ * herdb_create fails with HERDB_ERR_CUDA.
+ */
+#ifndef HERDB_H
+#define HERDB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "herdb_params.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct herdb_ctx herdb_ctx; /* opaque: devices, streams, device copies of keys */
+
+enum herdb_status {
+    HERDB_OK = 0,
+    HERDB_ERR_ARG = -1,      /* bad argument / malformed circuit                   */
+    HERDB_ERR_CUDA = -2,     /* CUDA runtime/driver error, or no device            */
+    HERDB_ERR_IO = -3,       /* key / partition file missing or malformed          */
+    HERDB_ERR_FORMAT = -4,   /* key blob / row payload does not match parameters   */
+    HERDB_ERR_NOKEY = -5,    /* no key loaded for the session                      */
+    HERDB_ERR_NOMEM = -6,
+    HERDB_ERR_UNSUPPORTED = -7
+};
+
+/* IWorkerGroup::TaskHandle::Status, same order (i_worker_group.hpp:18-24) */
+enum herdb_task_status { HERDB_TASK_COMPLETED = 0, HERDB_TASK_PENDING = 1,
+                         HERDB_TASK_TIME_OUT = 2, HERDB_TASK_ERROR = 3 };
+
+/* herd::common::DataType, same order (common/include/herd/common/model/data_type.hpp:9-22) */
+enum herdb_data_type { HERDB_BIT = 0, HERDB_UINT8, HERDB_UINT16, HERDB_UINT32, HERDB_UINT64,
+                       HERDB_INT8, HERDB_INT16, HERDB_INT32, HERDB_INT64 };
+
+/* herd::common::Operation, same order (operation.hpp:12-20) */
+enum herdb_operation { HERDB_OP_AND = 0, HERDB_OP_OR, HERDB_OP_NOT, HERDB_OP_XOR,
+                       HERDB_OP_NAND, HERDB_OP_MUX };
+
+enum herdb_node_kind { HERDB_NODE_INPUT = 0, HERDB_NODE_OUTPUT = 1,
+                       HERDB_NODE_CONSTANT = 2, HERDB_NODE_OPERATION = 3 };
+
+/* node_t (nodes.hpp:12-43): which fields are meaningful depends on kind */
+typedef struct herdb_node {
+    uint8_t  kind;        /* herdb_node_kind                                        */
+    uint8_t  op;          /* herdb_operation            (OPERATION)                 */
+    uint8_t  const_val;   /* 0/1                        (CONSTANT)                  */
+    uint8_t  reserved;
+    uint32_t tuple;       /* InputNode::tuple_index     (INPUT)                     */
+    uint32_t field;       /* field_index                (INPUT, OUTPUT)             */
+    uint32_t bit;         /* bit_index, LSB = 0         (INPUT, OUTPUT)             */
+} herdb_node;
+
+/* DAG edge parent -> child.  Operand order of a node = order in which its
+ * incoming edges appear in this array (DAG::parents(), dag.hpp:208-230).
+ * MUX operands are (select, value_if_1, value_if_0). */
+typedef struct herdb_edge { uint32_t from, to; } herdb_edge;
+
+/* Circuit (circuit.hpp:14-30): inputs[tuple][field] -> DataType, output[] -> DataType */
+typedef struct herdb_circuit {
+    const herdb_node* nodes;        size_t n_nodes;
+    const herdb_edge* edges;        size_t n_edges;
+    const uint8_t*  in_field_types;     /* DataType of every input field, tuples concatenated */
+    const uint32_t* in_tuple_offsets;   /* n_tuples + 1 offsets into in_field_types            */
+    size_t n_tuples;
+    const uint8_t*  out_field_types;    /* DataType per output column                          */
+    size_t n_out_fields;
+} herdb_circuit;
+
+typedef void (*herdb_done_fn)(void* user, int task_status /* herdb_task_status */);
+
+/* ------------------------------------------------------------------ lifecycle */
+int  herdb_create(herdb_ctx** out, const int* device_ids, int n_devices,
+                  const char* storage_dir, const char* key_dir);
+void herdb_destroy(herdb_ctx* ctx);
+const char* herdb_strerror(int code);
+const char* herdb_last_error(const herdb_ctx* ctx);
+int  herdb_device_count(const herdb_ctx* ctx);
+
+/* ------------------------------------------------------------------ keys
+ * load_key reads <key_dir>/<session>/<schema_type>.key (key_service.cpp:28-31);
+ * load_key_mem takes the same blob from host memory; load_key_dev takes it from
+ * device memory of ctx device `device` (e.g. after an NCCL broadcast done by the
+ * caller, one process per GPU).  With n_devices > 1 the blob is uploaded to
+ * device 0 and broadcast to the others over NVLink before conversion. */
+int herdb_load_key(herdb_ctx* ctx, const char* session_uuid, int schema_type);
+int herdb_load_key_mem(herdb_ctx* ctx, const char* session_uuid, const void* blob, size_t len);
+int herdb_load_key_dev(herdb_ctx* ctx, const char* session_uuid, int device,
+                       const void* d_blob, size_t len);
+int herdb_unload_key(herdb_ctx* ctx, const char* session_uuid);
+/* LWE dimension n of the session's key (ciphertext = n+1 u16 words) */
+int herdb_key_lwe_n(herdb_ctx* ctx, const char* session_uuid, uint32_t* n_out);
+
+/* ------------------------------------------------------------------ the task seam
+ * == IWorkerGroup::schedule_task(MapTask).  Returns immediately; `done` is
+ * invoked exactly once from a backend-owned host thread after the output
+ * partition file has been written and renamed into place (never from inside
+ * this call: executor.cpp:86-93 installs its callback after schedule_task
+ * returns). */
+int herdb_map_async(herdb_ctx* ctx, const char* session_uuid,
+                    const char* in_df_uuid, uint32_t in_partition, uint64_t row_count,
+                    const char* out_df_uuid, uint32_t out_partition,
+                    const herdb_circuit* circuit, herdb_done_fn done, void* user);
+/* blocks until every task scheduled so far has completed */
+int herdb_wait_idle(herdb_ctx* ctx);
+
+/* ------------------------------------------------------------------ file-less entry points
+ * Host buffers (the end-to-end path: H2D + evaluate + D2H).
+ * A ciphertext is (n+1) little-endian u16: a[0..n) then b, residues mod q=1024.
+ * A row is the concatenation of its bit-ciphertexts, fields in order, LSB first. */
+int herdb_eval_gate_batch(herdb_ctx* ctx, const char* session_uuid, int device, int gate /* herdb_gate */,
+                          const uint16_t* ct_a, const uint16_t* ct_b, uint16_t* ct_out, size_t batch);
+int herdb_eval_circuit_rows(herdb_ctx* ctx, const char* session_uuid, const herdb_circuit* circuit,
+                            const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows);
+/* Device-resident variants (inputs/outputs already in HBM of ctx device `device`;
+ * dense layout, ciphertext stride n+1 u16).  Work is enqueued on the backend's
+ * stream for that device and the call returns after synchronising it. */
+int herdb_eval_gate_batch_dev(herdb_ctx* ctx, const char* session_uuid, int device, int gate,
+                              const uint16_t* d_ct_a, const uint16_t* d_ct_b, uint16_t* d_ct_out,
+                              size_t batch);
+int herdb_eval_circuit_rows_dev(herdb_ctx* ctx, const char* session_uuid, int device,
+                                const herdb_circuit* circuit,
+                                const uint16_t* d_rows_in, uint16_t* d_rows_out, size_t n_rows);
+
+/* circuit facts (host-only, no device needed): bootstrapped gates per row, levels, slots */
+typedef struct herdb_circuit_info {
+    uint32_t in_bits, out_bits;     /* ciphertexts per input / output row                      */
+    uint32_t boot_gates;            /* bootstraps per row after lowering XOR/MUX               */
+    uint32_t levels;                /* dependent bootstrap levels                              */
+    uint32_t max_level_width;       /* widest level (gates)                                    */
+    uint32_t slots;                 /* ciphertext slots per row after liveness reuse           */
+} herdb_circuit_info;
+int herdb_circuit_analyze(const herdb_circuit* circuit, herdb_circuit_info* info);
+
+/* ------------------------------------------------------------------ measurement hooks */
+typedef struct herdb_stats {
+    uint64_t kernel_launches;       /* our kernels launched since create / last reset          */
+    uint64_t gates_bootstrapped;
+    double   blind_rotate_ms;       /* CUDA-event time of blind-rotate launches (sum)          */
+    double   keyswitch_ms;          /* CUDA-event time of key-switch launches (sum)            */
+    uint64_t blind_rotate_launches, keyswitch_launches;
+    uint64_t h2d_bytes, d2h_bytes;
+} herdb_stats;
+int herdb_get_stats(herdb_ctx* ctx, int device, herdb_stats* out);
+int herdb_reset_stats(herdb_ctx* ctx);
+/* raw integer-pipe peak microbenchmark (IMAD / IADD3 / IMAD.HI / IMAD.WIDE), Tops/s */
+int herdb_measure_int_peak(herdb_ctx* ctx, int device, double* imad_tops, double* iadd3_tops,
+                           double* imadhi_tops, double* imadwide_tops, double* mixed_tops);
+
+/* ------------------------------------------------------------------ client stand-in
+ * herdsman never sees secret keys; the herd client (libherd, not in the
+ * reference tree) generates keys and encrypts rows.  These host-only helpers
+ * produce synthetic keys / ciphertexts in the flat formats of herdb_params.h so
+ * benchmarks and tests have inputs.  They are NOT on the evaluation path. */
+size_t herdb_client_key_blob_size(uint32_t n);
+int herdb_client_keygen(uint32_t n, uint64_t seed, int8_t* sk_lwe /* n */, int8_t* sk_ring /* N */,
+                        void* blob, size_t blob_len);
+int herdb_client_encrypt_bits(uint32_t n, const int8_t* sk_lwe, uint64_t seed, uint64_t first_ct_index,
+                              const uint8_t* bits, size_t count, uint16_t* cts);
+int herdb_client_decrypt_bits(uint32_t n, const int8_t* sk_lwe, const uint16_t* cts, size_t count,
+                              uint8_t* bits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HERDB_H */
