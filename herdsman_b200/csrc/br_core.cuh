@@ -1,0 +1,270 @@
+// br_core.cuh -- the programmable-bootstrap body executed by one CTA (256 threads) for a
+// group of kC = 4 ciphertexts that share every bootstrapping-key read.
+//
+// Replaces, for the hot path of herdsman's map tasks (MapTask -> per-row EvalBinGate), the
+// OpenFHE binfhe v1.0.x routines restated in oracle/oracle.c:
+//   EvalBinGate ciphertext preparation, BootstrapGateCore (accumulator init),
+//   RingGSWAccumulatorCGGI::EvalAcc / AddToAccCGGI (the CMUX loop), SignedDigitDecompose,
+//   Transpose + sample extraction and ModSwitch(Q -> qKS)            (SURVEY.md 8a a7-a12).
+// Key switching + ModSwitch(qKS -> q) is keyswitch.cu.
+//
+// Data residency (per CTA, shared memory):
+//   acc  [kC][2][1024] u32   accumulator, NTT domain, pre-scaled by 1/N, canonical [0,Q)
+//   dig  [kC][8][1024] u32   NTT of the 8 signed-digit polynomials, lazy residues < 2^32
+//   itw  [16][32][4]   u32   per-lane twiddles of the inverse pass 1
+//   lwe  [kC][n+1]     u16   prepared LWE ciphertext (ct1 + ct2 etc.)
+// Per step: phase A = one warp per (ciphertext, component): INTT, decompose, 4 forward NTTs;
+//           phase B = one thread per 4 evaluation points: 32 key words (128-bit loads from
+//           L2, shared by the 4 ciphertexts) x 8 digits multiply-accumulated exactly in 64
+//           bits, folded, multiplied by the two monomials and added into acc.
+//
+// The body is templated on an execution environment so that tests/emu can run the very same
+// code on the CPU with host threads and barriers (there is no GPU in the build container).
+#pragma once
+#include "ntt_core.cuh"
+
+namespace herdb {
+
+constexpr int kC = 4;                       // ciphertexts per CTA
+constexpr int kThreads = 256;               // 8 warps = kC * 2 polynomials
+constexpr u32 kExtStride = 1032;            // u16 words per extracted ciphertext (N + 1, padded to 16 B)
+constexpr u32 kLweMax = HERDB_N_STD128;     // largest LWE dimension supported by the smem layout
+
+enum OperandFlags : uint8_t { kOpNeg = 1, kOpConst = 2, kOpConstVal = 4 };
+
+// one bootstrapped gate of a circuit level; a job = (gate, row)
+struct GateDesc {
+    uint8_t gate;                // herdb_gate
+    uint8_t flag_a, flag_b;      // OperandFlags
+    uint8_t pool_a, pool_b, pool_out;
+    uint8_t pad[2];
+    u32 idx_a, idx_b, idx_out;   // ciphertext index inside a row of the pool
+};
+struct Pool { u16* base; u32 row_cts; u32 pad; };    // ciphertext (r, idx) at base + (r*row_cts + idx)*(n+1)
+
+struct BrParams {
+    const u32* bsk;              // [n][2 sign][8 rows][2 cols][1024]  NTT domain, * 1/N, canonical
+    const u32* mono;             // [1024][1024]   NTT(X^(2*row) - 1), canonical
+    const u32* ftw2;             // [16][32][4]    forward pass-2 lane twiddles
+    const u32* itw1;             // [16][32][4]    inverse pass-1 lane twiddles
+    const GateDesc* gates;       // gates of this level
+    Pool pools[4];
+    u16* ext;                    // [jobs][kExtStride]  extracted, mod-switched (qKS) ciphertexts
+    u32* trace;                  // optional debug: [jobs][2][1024] accumulator (coefficient domain) after `steps`
+    u32 n;                       // LWE dimension
+    u32 steps;                   // CMUX steps to run (== n except in debug traces)
+    u32 rows;                    // rows in this chunk
+    u32 jobs;                    // gates_in_level * rows;  job -> gate = job / rows, row = job % rows
+};
+
+struct BrSmem {
+    u32 acc[kC][2][kN];
+    u32 dig[kC][kDG2][kN];
+    u32 itw[kLaneTwWords];
+    u16 lwe[kC][kLweMax + 8];
+    u32 gate_b[kC];              // prepared b and gate code per ciphertext
+    u32 gate_code[kC];
+};
+
+constexpr u32 kAccInitPos = cmulmod(kQ / 8 + 1, kNInv);             // +(Q/8+1) / N
+constexpr u32 kAccInitNeg = cmulmod(kQ - (kQ / 8 + 1), kNInv);      // -(Q/8+1) / N
+constexpr u32 kGateConstEighths[6] = {5, 7, 1, 3, 5, 1};            // OR AND NOR NAND XOR_FAST XNOR_FAST
+
+HERDB_HD u32 gate_const_eighths(u32 gate) {
+    // RingGSWCryptoParams::m_gateConst = {5,7,1,3,5,1} * q/8
+    return gate == 0 ? 5u : gate == 1 ? 7u : gate == 2 ? 1u : gate == 3 ? 3u : gate == 4 ? 5u : 1u;
+}
+
+// one LWE word of an operand after the free transforms (EvalNOT / trivial constant)
+HERDB_HD u32 operand_word(const Pool* pools, u32 pool, u32 idx, u32 flags, u32 row, u32 n, u32 k) {
+    if (flags & kOpConst) return k == n ? ((flags & kOpConstVal) ? kLweQ / HERDB_PT_MOD : 0u) : 0u;
+    u32 v = pools[pool].base[((size_t)row * pools[pool].row_cts + idx) * (n + 1) + k];
+    if (flags & kOpNeg) v = (k == n) ? ((kLweQ >> 2) + kLweQ - v) & (kLweQ - 1) : (kLweQ - v) & (kLweQ - 1);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+template <class Env>
+HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 group) {
+    const u32 tid = env.tid();
+    const u32 lane = tid & 31, warp = tid >> 5;
+    const u32 n = P.n;
+
+    // ---- ciphertext preparation: ct1 + ct2 (2*(ct1 - ct2) for XOR_FAST / XNOR_FAST), NOT folded in
+    for (int c = 0; c < kC; ++c) {
+        u32 job = group * kC + c; if (job >= P.jobs) job = P.jobs - 1;
+        const GateDesc g = P.gates[job / P.rows];
+        const u32 row = job % P.rows;
+        for (u32 k = tid; k <= n; k += kThreads) {
+            u32 a = operand_word(P.pools, g.pool_a, g.idx_a, g.flag_a, row, n, k);
+            u32 b = operand_word(P.pools, g.pool_b, g.idx_b, g.flag_b, row, n, k);
+            u32 v = (g.gate >= HERDB_GATE_XOR_FAST) ? (2u * (a + kLweQ - b)) & (kLweQ - 1) : (a + b) & (kLweQ - 1);
+            if (k == n) { S.gate_b[c] = v; S.gate_code[c] = g.gate; } else S.lwe[c][k] = (u16)v;
+        }
+    }
+    // inverse pass-1 lane twiddles -> smem (once per group; 8 KB)
+    for (u32 w = tid; w < kLaneTwWords; w += kThreads) S.itw[w] = P.itw1[w];
+    // forward pass-2 lane twiddles -> registers (31 pairs per lane)
+    u32 ftw[62];
+#pragma unroll
+    for (int p = 0; p < 31; ++p) {
+        ftw[2 * p] = P.ftw2[((p >> 1) * 32 + lane) * 4 + (p & 1) * 2];
+        ftw[2 * p + 1] = P.ftw2[((p >> 1) * 32 + lane) * 4 + (p & 1) * 2 + 1];
+    }
+    env.sync();
+
+    // ---- BootstrapGateCore: acc = (0, NTT(m)), m[2j] = +-(Q/8+1) depending on (b - j) in [q1, q2)
+    {
+        const int c = warp >> 1, j = warp & 1;
+        u32 x[32];
+        if (j == 0) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) x[k] = 0;
+            store_contig(S.acc[c][0], lane, x);
+        } else {
+            const u32 b = S.gate_b[c];
+            const u32 q1 = gate_const_eighths(S.gate_code[c]) * (kLweQ >> 3);
+            const u32 q2 = (q1 + (kLweQ >> 1)) & (kLweQ - 1);
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                const u32 coef = lane + 32 * k;                        // coefficient index; factor 2N/q = 2
+                const u32 temp = (b + kLweQ - (coef >> 1)) & (kLweQ - 1);
+                const bool in = (q1 < q2) ? (temp >= q1 && temp < q2) : !(temp >= q2 && temp < q1);
+                x[k] = (coef & 1) ? 0u : (in ? kAccInitNeg : kAccInitPos);
+            }
+            fwd_pass1(x);
+            store_strided(S.dig[c][1], lane, x);
+            env.syncwarp();
+            load_contig(S.dig[c][1], lane, x);
+            fwd_pass2(x, ftw);
+#pragma unroll
+            for (int k = 0; k < 32; ++k) x[k] = canon32(x[k]);
+            store_contig(S.acc[c][1], lane, x);
+        }
+    }
+    env.sync();
+
+    // ---- EvalAcc: n CMUX steps (AddToAccCGGI)
+    for (u32 i = 0; i < P.steps; ++i) {
+        // ===== phase A: warp = (ciphertext c, component j)
+        {
+            const int c = warp >> 1, j = warp & 1;
+            u32 x[32];
+            load_contig(S.acc[c][j], lane, x);
+            inv_pass1(x, S.itw, lane);
+            store_contig(S.dig[c][j], lane, x);              // dig[c][j] doubles as transposition scratch
+            env.syncwarp();
+            load_strided(S.dig[c][j], lane, x);
+            inv_pass2(x);
+            int d[32];                                        // SignedDigitDecompose: centred representative
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                u32 t = csub(x[k], kQ);                       // canonical [0, Q)
+                d[k] = (t < (kQ >> 1)) ? (int)t : (int)t - (int)kQ;
+            }
+            env.syncwarp();                                   // all lanes done reading the scratch
+#pragma unroll
+            for (int l = 0; l < (int)kDG; ++l) {
+#pragma unroll
+                for (int k = 0; k < 32; ++k) {
+                    int r = (int)((u32)d[k] << 25) >> 25;     // signed low 7 bits
+                    d[k] = (d[k] - r) >> 7;
+                    x[k] = (u32)(r + (int)kQ);                // r mod Q, lazily in [Q-64, Q+63]
+                }
+                u32* out = S.dig[c][j + 2 * l];               // output polynomial index j + 2*l
+                fwd_pass1(x);
+                store_strided(out, lane, x);
+                env.syncwarp();
+                load_contig(out, lane, x);
+                fwd_pass2(x, ftw);
+                store_contig(out, lane, x);                   // < 22Q + 2Q < 2^32, not reduced
+            }
+        }
+        env.sync();
+        // ===== phase B: thread = evaluation points 4*tid .. 4*tid+3
+        {
+            const u32 phys = swz(4 * tid);
+            const u32* K = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
+            u64 mac[kC][2][2][4];
+#pragma unroll
+            for (int c = 0; c < kC; ++c)
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int jo = 0; jo < 2; ++jo)
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) mac[c][s][jo][p] = 0;
+#pragma unroll
+            for (int r = 0; r < (int)kDG2; ++r) {
+                V4 kv[2][2];
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int jo = 0; jo < 2; ++jo) kv[s][jo] = env.ldg_v4(K + ((s * kDG2 + r) * 2 + jo) * kN);
+#pragma unroll
+                for (int c = 0; c < kC; ++c) {
+                    V4 dv = *reinterpret_cast<const V4*>(&S.dig[c][r][phys]);
+#pragma unroll
+                    for (int s = 0; s < 2; ++s)
+#pragma unroll
+                        for (int jo = 0; jo < 2; ++jo)
+#pragma unroll
+                            for (int p = 0; p < 4; ++p) mac[c][s][jo][p] += (u64)dv.v[p] * kv[s][jo].v[p];
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < kC; ++c) {
+                const u32 a = S.lwe[c][i];
+                const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
+                const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
+                V4 mp = env.ldg_v4(P.mono + (size_t)row_pos * kN + 4 * tid);
+                V4 mn = env.ldg_v4(P.mono + (size_t)row_neg * kN + 4 * tid);
+#pragma unroll
+                for (int jo = 0; jo < 2; ++jo) {
+                    V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys]);
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) {
+                        u32 rp = fold62(mac[c][0][jo][p]);
+                        u32 rn = fold62(mac[c][1][jo][p]);
+                        u32 y = fold62((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
+                        av.v[p] = canon32(av.v[p] + y);
+                    }
+                    *reinterpret_cast<V4*>(&S.acc[c][jo][phys]) = av;
+                }
+            }
+        }
+        env.sync();
+    }
+
+    // ---- back to coefficients, Transpose(acc[0]) -> LWE a, acc[1][0] + Q/8 + 1 -> b, ModSwitch(qKS)
+    {
+        const int c = warp >> 1, j = warp & 1;
+        const u32 job = group * kC + c;
+        u32 x[32];
+        load_contig(S.acc[c][j], lane, x);
+        inv_pass1(x, S.itw, lane);
+        store_contig(S.dig[c][j], lane, x);
+        env.syncwarp();
+        load_strided(S.dig[c][j], lane, x);
+        inv_pass2(x);
+        if (job < P.jobs) {
+            u16* ext = P.ext + (size_t)job * kExtStride;
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+                const u32 coef = lane + 32 * k;
+                const u32 v = csub(x[k], kQ);
+                if (P.trace) P.trace[((size_t)job * 2 + j) * kN + coef] = v;
+                if (j == 0) {       // a'(0) = a(0), a'(N - k) = -a(k)
+                    const u32 t = (coef == 0) ? v : (v == 0 ? 0u : kQ - v);
+                    ext[(kN - coef) & (kN - 1)] = (u16)modswitch_Q_to_qKS(t);
+                } else if (coef == 0) {
+                    u32 bsum = v + (kQ / 8 + 1); if (bsum >= kQ) bsum -= kQ;
+                    ext[kN] = (u16)modswitch_Q_to_qKS(bsum);
+                }
+            }
+        }
+    }
+    env.sync();      // smem is reused by the next group
+}
+
+}  // namespace herdb

@@ -1,0 +1,210 @@
+// kernels.cu -- hand-written sm_100a kernels of the gate-evaluation hot path.
+//
+//   blind_rotate_kernel   K1+K2+K3 of SURVEY.md 2.1: ciphertext prep, accumulator init, the n
+//                         CMUX steps, sample extraction and ModSwitch(Q->qKS)   (br_core.cuh)
+//   keyswitch_kernel      K4: LWE key switch (OpenFHE LWEEncryptionScheme::KeySwitch) + ModSwitch(qKS->q)
+//   gather_outputs_kernel OutputNode handling: copies / NOTs / constants into the output rows
+//   bsk_convert_kernel    key load: coefficient-domain RGSW rows -> NTT domain, * 1/N
+//   ksk_relayout_kernel   key load: pads key-switch rows to a 16-byte multiple
+//   int_peak_kernel       measurement: raw IMAD / IADD3 / IMAD.HI / IMAD.WIDE issue rates
+//
+// Integer pipes only (IMAD / IMAD.HI / IMAD.WIDE / IADD3 / LOP3): the work is exact modular
+// arithmetic, there is no tensor-core formulation (BASELINE.json north_star).
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "br_core.cuh"
+#include "kernels.h"
+
+namespace herdb {
+
+struct DevEnv {
+    __device__ __forceinline__ u32 tid() const { return threadIdx.x; }
+    __device__ __forceinline__ void sync() { __syncthreads(); }
+    __device__ __forceinline__ void syncwarp() { __syncwarp(); }
+    __device__ __forceinline__ V4 ldg_v4(const u32* p) const {
+        uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+        V4 r; r.v[0] = q.x; r.v[1] = q.y; r.v[2] = q.z; r.v[3] = q.w;
+        return r;
+    }
+};
+
+// one CTA per SM (176 KB of shared memory), persistent over groups of kC jobs
+__global__ void __launch_bounds__(kThreads, 1) blind_rotate_kernel(const __grid_constant__ BrParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BrSmem& S = *reinterpret_cast<BrSmem*>(smem_raw);
+    DevEnv env;
+    const u32 groups = (P.jobs + kC - 1) / kC;
+    for (u32 g = blockIdx.x; g < groups; g += gridDim.x) blind_rotate_group(env, P, S, g);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Key switch: a_out = -sum_{i,j} KSK_A[i][digit_j(a_i)][j], b_out = b - sum KSK_B[...]  (mod qKS),
+// then ModSwitch to q.  One CTA per job; thread w owns the u16 pair (2w, 2w+1) of the padded row.
+// Row sums are accumulated per 16-bit half in 32 bits (2048 rows * 2^14 < 2^25).
+__global__ void __launch_bounds__(288) keyswitch_kernel(const __grid_constant__ KsParams P) {
+    __shared__ u16 ext_s[kExtStride];
+    const u32 words = P.ks_stride >> 1;
+    const u32* ksk32 = reinterpret_cast<const u32*>(P.ksk);
+    for (u32 job = blockIdx.x; job < P.jobs; job += gridDim.x) {
+        __syncthreads();
+        for (u32 k = threadIdx.x; k < kExtStride / 2; k += blockDim.x)
+            reinterpret_cast<u32*>(ext_s)[k] = reinterpret_cast<const u32*>(P.ext + (size_t)job * kExtStride)[k];
+        __syncthreads();
+        const u32 w = threadIdx.x;
+        if (w < words) {
+            u32 lo = 0, hi = 0;
+#pragma unroll 8
+            for (u32 i = 0; i < kN; ++i) {
+                const u32 t = ext_s[i];
+                const u32 r0 = ((i * kBaseKS + (t & (kBaseKS - 1))) * kDKS + 0);
+                const u32 r1 = ((i * kBaseKS + (t >> HERDB_BASEKS_LOG)) * kDKS + 1);
+                const u32 w0 = __ldg(ksk32 + (size_t)r0 * words + w);
+                const u32 w1 = __ldg(ksk32 + (size_t)r1 * words + w);
+                lo += (w0 & 0xFFFFu) + (w1 & 0xFFFFu);
+                hi += (w0 >> 16) + (w1 >> 16);
+            }
+            const GateDesc g = P.gates[job / P.rows];
+            const u32 row = job % P.rows;
+            u16* out = P.pools[g.pool_out].base + ((size_t)row * P.pools[g.pool_out].row_cts + g.idx_out) * (P.n + 1);
+            const u32 k0 = 2 * w, k1 = 2 * w + 1;
+            if (k0 <= P.n) {
+                u32 v = (k0 == P.n ? (u32)ext_s[kN] - lo : 0u - lo) & (kQKS - 1);
+                out[k0] = (u16)modswitch_qKS_to_q(v);
+            }
+            if (k1 <= P.n) {
+                u32 v = (k1 == P.n ? (u32)ext_s[kN] - hi : 0u - hi) & (kQKS - 1);
+                out[k1] = (u16)modswitch_qKS_to_q(v);
+            }
+        }
+    }
+}
+
+// OutputNode: rows_out[row][o] = operand (with NOT / constant folding applied)
+__global__ void gather_outputs_kernel(const __grid_constant__ GatherParams P) {
+    const u32 w = P.n + 1;
+    const size_t total = (size_t)P.rows * P.out_bits * w;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const u32 k = (u32)(t % w);
+        const size_t ct = t / w;
+        const u32 o = (u32)(ct % P.out_bits), row = (u32)(ct / P.out_bits);
+        const OutDesc d = P.outs[o];
+        P.rows_out[t] = (u16)operand_word(P.pools, d.pool, d.idx, d.flags, row, P.n, k);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// key load
+__global__ void __launch_bounds__(256) bsk_convert_kernel(const u32* __restrict__ in, u32* __restrict__ out,
+                                                          const u32* __restrict__ ftw2, u32 polys) {
+    __shared__ __align__(16) u32 scratch[8][kN];
+    const u32 lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    u32 ftw[62];
+#pragma unroll
+    for (int p = 0; p < 31; ++p) {
+        ftw[2 * p] = ftw2[((p >> 1) * 32 + lane) * 4 + (p & 1) * 2];
+        ftw[2 * p + 1] = ftw2[((p >> 1) * 32 + lane) * 4 + (p & 1) * 2 + 1];
+    }
+    for (u32 poly = blockIdx.x * 8 + warp; poly < polys; poly += gridDim.x * 8) {
+        u32 x[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) x[k] = in[(size_t)poly * kN + lane + 32 * k];
+        fwd_pass1(x);
+        __syncwarp();
+        store_strided(scratch[warp], lane, x);
+        __syncwarp();
+        load_contig(scratch[warp], lane, x);
+        fwd_pass2(x, ftw);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) x[e] = canon32(mul_shoup_lazy(kNInv, kNInvShoup, x[e]));
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            uint4 q = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+            *reinterpret_cast<uint4*>(out + (size_t)poly * kN + 32 * lane + 4 * c) = q;
+        }
+    }
+}
+
+__global__ void ksk_relayout_kernel(const u16* __restrict__ in, u16* __restrict__ out, u32 n, u32 stride, size_t rows) {
+    const size_t total = rows * stride;
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = t / stride; const u32 k = (u32)(t % stride);
+        out[t] = k <= n ? in[r * (n + 1) + k] : (u16)0;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// integer-pipe peak: 8 independent dependency chains per thread, 4096 iterations
+template <int MODE>
+__global__ void __launch_bounds__(256) int_peak_kernel(u32* out, u32 seed, int iters) {
+    u32 a[8], b = seed | 1u, c = seed * 2654435761u + threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = threadIdx.x * 97u + i * 13u + seed;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (MODE == 0) a[i] = a[i] * b + c;                                     // IMAD
+                else if (MODE == 1) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(c));   // IADD3
+                else if (MODE == 2) a[i] = __umulhi(a[i], b) + c;                       // IMAD.HI
+                else if (MODE == 3) {                                                   // IMAD.WIDE
+                    u64 t = (u64)a[i] * b + (((u64)c << 32) | a[i]);
+                    a[i] = (u32)t ^ (u32)(t >> 32);
+                } else {                                                                 // Shoup butterfly mix
+                    u32 q = __umulhi(a[i], b); u32 v = a[i] * c - q * kQ; a[i] = a[(i + 1) & 7] + v;
+                }
+            }
+        }
+    }
+    u32 r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r ^= a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers (plain C++ signatures so backend.cpp does not need nvcc)
+cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream) {
+    // per device attribute; cheap enough to set on every launch (launches last milliseconds)
+    cudaError_t e = cudaFuncSetAttribute(blind_rotate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BrSmem));
+    if (e != cudaSuccess) return e;
+    const u32 groups = (P.jobs + kC - 1) / kC;
+    if (!groups) return cudaSuccess;
+    const u32 grid = groups < (u32)sm_count ? groups : (u32)sm_count;
+    blind_rotate_kernel<<<grid, kThreads, sizeof(BrSmem), stream>>>(P);
+    return cudaGetLastError();
+}
+cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream) {
+    if (!P.jobs) return cudaSuccess;
+    const u32 words = P.ks_stride >> 1;
+    const u32 threads = ((words + 31) / 32) * 32;
+    const u32 max_grid = (u32)sm_count * 16;
+    const u32 grid = P.jobs < max_grid ? P.jobs : max_grid;
+    keyswitch_kernel<<<grid, threads, 0, stream>>>(P);
+    return cudaGetLastError();
+}
+cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream) {
+    if (!P.rows || !P.out_bits) return cudaSuccess;
+    gather_outputs_kernel<<<sm_count * 8, 256, 0, stream>>>(P);
+    return cudaGetLastError();
+}
+cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 polys, int sm_count, cudaStream_t stream) {
+    bsk_convert_kernel<<<sm_count * 2, 256, 0, stream>>>(in, out, ftw2, polys);
+    return cudaGetLastError();
+}
+cudaError_t launch_ksk_relayout(const u16* in, u16* out, u32 n, u32 stride, size_t rows, int sm_count, cudaStream_t stream) {
+    ksk_relayout_kernel<<<sm_count * 8, 256, 0, stream>>>(in, out, n, stride, rows);
+    return cudaGetLastError();
+}
+cudaError_t launch_int_peak(int mode, u32* out, int blocks, int iters, cudaStream_t stream) {
+    switch (mode) {
+    case 0: int_peak_kernel<0><<<blocks, 256, 0, stream>>>(out, 12345u, iters); break;
+    case 1: int_peak_kernel<1><<<blocks, 256, 0, stream>>>(out, 12345u, iters); break;
+    case 2: int_peak_kernel<2><<<blocks, 256, 0, stream>>>(out, 12345u, iters); break;
+    case 3: int_peak_kernel<3><<<blocks, 256, 0, stream>>>(out, 12345u, iters); break;
+    default: int_peak_kernel<4><<<blocks, 256, 0, stream>>>(out, 12345u, iters); break;
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace herdb

@@ -1,0 +1,136 @@
+// modarith.cuh -- 32-bit lazy modular arithmetic over Z_Q, Q = 2^27 - 2^11 + 1, and the
+// compile-time twiddle tables of the negacyclic NTT (N = 1024).
+//
+// Replaces (on the integer pipes of sm_100a) OpenFHE's NativeInteger ModMulFastConst /
+// ModAddFast / ModSubFast used by binfhe's AddToAccCGGI.
+// Everything here is exact: values are kept as lazily reduced residues in u32 and every
+// function documents the range it accepts and returns.
+//
+// Host/device: the same source is compiled by g++ for the CPU emulation test
+// (tests/emu) and by nvcc for the kernels.
+#pragma once
+#include <stdint.h>
+#include "../../include/herdb_params.h"
+
+#if defined(__CUDACC__)
+#define HERDB_HD __host__ __device__ __forceinline__
+#define HERDB_D __device__ __forceinline__
+#else
+#define HERDB_HD inline
+#define HERDB_D inline
+#endif
+
+namespace herdb {
+
+typedef uint16_t u16;
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+constexpr u32 kQ = HERDB_Q;
+constexpr u32 kQ2 = 2u * HERDB_Q;
+constexpr u32 kN = HERDB_RING_N;
+constexpr u32 kLogN = HERDB_RING_LOGN;
+constexpr u32 kDG = HERDB_DIGITS_G;
+constexpr u32 kDG2 = 2u * HERDB_DIGITS_G;
+constexpr u32 kLweQ = HERDB_LWE_Q;
+constexpr u32 kQKS = HERDB_QKS;
+constexpr u32 kBaseKS = 1u << HERDB_BASEKS_LOG;
+constexpr u32 kDKS = HERDB_DIGITS_KS;
+constexpr u32 kPsi = 282116u;            // minimum primitive 2N-th root of unity mod Q (checked in tests)
+
+static_assert(kQ == (1u << 27) - (1u << 11) + 1u, "kernels are specialised for Q = 2^27 - 2^11 + 1");
+static_assert(kN == 1024 && kLweQ == 1024, "kernels are specialised for N = q = 1024");
+
+// ---------------------------------------------------------------- constexpr helpers (host side / compile time)
+constexpr u32 cmulmod(u64 a, u64 b) { return (u32)((a * b) % kQ); }
+constexpr u32 cpowmod(u64 b, u64 e) {
+    u64 r = 1; b %= kQ;
+    while (e) { if (e & 1) r = (r * b) % kQ; b = (b * b) % kQ; e >>= 1; }
+    return (u32)r;
+}
+constexpr u32 cbitrev10(u32 x) {
+    u32 r = 0;
+    for (int i = 0; i < 10; ++i) { r = (r << 1) | (x & 1); x >>= 1; }
+    return r;
+}
+constexpr u32 cshoup(u32 w) { return (u32)(((u64)w << 32) / kQ); }
+constexpr u32 kPsiInv = cpowmod(kPsi, 2 * kN - 1);
+constexpr u32 kNInv = cpowmod(kN, kQ - 2);
+constexpr u32 kNInvShoup = cshoup(kNInv);
+static_assert(cpowmod(kPsi, kN) == kQ - 1, "psi must be a primitive 2N-th root");
+static_assert(cmulmod(kNInv, kN) == 1, "N^-1");
+// forward twiddle k: psi^bitrev(k); inverse twiddle k: psi^-bitrev(k)
+constexpr u32 ctw_fwd(u32 k) { return cpowmod(kPsi, cbitrev10(k)); }
+constexpr u32 ctw_inv(u32 k) { return cpowmod(kPsiInv, cbitrev10(k)); }
+
+// 2^31 mod Q and its Shoup companion: folds the high part of a 62-bit value
+constexpr u32 kR31 = (u32)((1ull << 31) % kQ);
+constexpr u32 kR31s = cshoup(kR31);
+
+// Stages whose twiddle depends only on the register index (not on the lane) read their
+// (w, w') pairs from constant memory: the operand folds into IMAD/IMAD.HI as c[bank][imm].
+struct UniformTw { u32 v[32][2]; };
+constexpr UniformTw make_uniform_fwd() {
+    UniformTw t{};
+    for (u32 k = 1; k < 32; ++k) { t.v[k][0] = ctw_fwd(k); t.v[k][1] = cshoup(t.v[k][0]); }
+    return t;
+}
+constexpr UniformTw make_uniform_inv() {
+    UniformTw t{};
+    for (u32 k = 1; k < 32; ++k) { t.v[k][0] = ctw_inv(k); t.v[k][1] = cshoup(t.v[k][0]); }
+    return t;
+}
+#if defined(__CUDACC__)
+__constant__ UniformTw c_tw_fwd = make_uniform_fwd();
+__constant__ UniformTw c_tw_inv = make_uniform_inv();
+#endif
+static constexpr UniformTw h_tw_fwd = make_uniform_fwd();
+static constexpr UniformTw h_tw_inv = make_uniform_inv();
+
+#if defined(__CUDA_ARCH__)
+#define HERDB_TWF(k, i) c_tw_fwd.v[k][i]
+#define HERDB_TWI(k, i) c_tw_inv.v[k][i]
+#else
+#define HERDB_TWF(k, i) h_tw_fwd.v[k][i]
+#define HERDB_TWI(k, i) h_tw_inv.v[k][i]
+#endif
+
+// ---------------------------------------------------------------- run-time primitives
+HERDB_HD u32 mulhi32(u32 a, u32 b) {
+#if defined(__CUDA_ARCH__)
+    return __umulhi(a, b);
+#else
+    return (u32)(((u64)a * b) >> 32);
+#endif
+}
+HERDB_HD u32 umin32(u32 a, u32 b) { return a < b ? a : b; }
+
+// w*y mod Q, lazily: any y < 2^32, w < Q, wp = floor(w*2^32/Q); result in [0, 2Q)
+HERDB_HD u32 mul_shoup_lazy(u32 w, u32 wp, u32 y) {
+    u32 q = mulhi32(wp, y);
+    return w * y - q * kQ;
+}
+// x >= m ? x - m : x   (for x < 2m): unsigned wrap makes x-m huge when x < m
+HERDB_HD u32 csub(u32 x, u32 m) { return umin32(x, x - m); }
+// any x < 2^32 -> canonical residue in [0, Q): x - (x>>27)*Q lands in [0, 2Q) because
+// x - (x>>27)*Q = (x mod 2^27) + 2047*(x>>27) < 2^27 + 2047*31 < 2Q
+HERDB_HD u32 canon32(u32 x) { return csub(x - (x >> 27) * kQ, kQ); }
+// any x < 2^62 -> residue < 2Q + 2^31 < 2^32 (not canonical)
+HERDB_HD u32 fold62(u64 x) {
+    u32 hi = (u32)(x >> 31), lo = (u32)x & 0x7FFFFFFFu;
+    return mul_shoup_lazy(kR31, kR31s, hi) + lo;
+}
+// bank-conflict-free layout of a 1024-word polynomial in shared memory: word x lives at
+// swz(x); rows of 32 words, the 16-byte chunk index is XORed with the row index
+HERDB_HD u32 swz(u32 x) { return x ^ (((x >> 5) & 7u) << 2); }
+
+// LWE mod switch Q -> qKS = 2^14 (OpenFHE RoundqQ, integer form): floor((2*v*qKS + Q) / 2Q) mod qKS
+HERDB_HD u32 modswitch_Q_to_qKS(u32 v) {
+    return (u32)((((u64)v << 15) + kQ) / (2ull * kQ)) & (kQKS - 1);
+}
+// qKS -> q = 2^10: floor(v/16 + 0.5) mod q
+HERDB_HD u32 modswitch_qKS_to_q(u32 v) { return ((v + 8u) >> 4) & (kLweQ - 1); }
+
+struct alignas(16) V4 { u32 v[4]; };
+
+}  // namespace herdb

@@ -1,0 +1,139 @@
+// ntt_core.cuh -- register-resident negacyclic NTT of one 1024-coefficient polynomial by
+// one warp: 32 coefficients per lane, two passes of five radix-2 stages each, one
+// shared-memory transposition between the passes (swizzled, bank-conflict free).
+//
+// Replaces OpenFHE's ChineseRemainderTransformFTT<NativeVector>::ForwardTransformToBitReverse
+// / InverseTransformFromBitReverse.  Forward = Cooley-Tukey, natural in,
+// bit-reversed out; inverse = Gentleman-Sande, bit-reversed in, natural out.  The 1/N of
+// the inverse is NOT applied here: it is folded into the bootstrapping key at load time.
+//
+// Lane layouts (T = lane id):
+//   "strided"    x[k] <-> coefficient T + 32*k   (stages with stride >= 32: twiddle depends on k only)
+//   "contiguous" x[e] <-> coefficient 32*T + e   (stages with stride <= 16: per-lane twiddles)
+#pragma once
+#include "modarith.cuh"
+
+namespace herdb {
+
+// per-lane twiddle tables, [16 chunks][32 lanes][4 words]: chunk g of lane T holds the
+// (w, w') pairs 2g and 2g+1 of that lane's 31-pair list (pair 31 is padding)
+constexpr u32 kLaneTwWords = 16 * 32 * 4;
+// forward pass 2 list order: stage s=5 (1 pair), s=6 (2), s=7 (4), s=8 (8), s=9 (16)
+// inverse pass 1 list order: t=1 (16 pairs), t=2 (8), t=4 (4), t=8 (2), t=16 (1)
+inline void build_lane_twiddles(u32* fwd2, u32* inv1) {
+    for (u32 T = 0; T < 32; ++T) {
+        u32 fl[32][2] = {}, il[32][2] = {};
+        u32 p = 0;
+        for (u32 s = 5; s < 10; ++s) {
+            u32 t = 16u >> (s - 5);
+            for (u32 i = 0; i < 16 / t; ++i, ++p) {
+                fl[p][0] = ctw_fwd((1u << s) + T * (16 / t) + i);
+                fl[p][1] = cshoup(fl[p][0]);
+            }
+        }
+        p = 0;
+        for (u32 t = 1; t <= 16; t <<= 1)
+            for (u32 i = 0; i < 16 / t; ++i, ++p) {
+                il[p][0] = ctw_inv(512 / t + T * (16 / t) + i);
+                il[p][1] = cshoup(il[p][0]);
+            }
+        for (u32 g = 0; g < 16; ++g)
+            for (u32 w = 0; w < 4; ++w) {
+                fwd2[(g * 32 + T) * 4 + w] = fl[2 * g + (w >> 1)][w & 1];
+                inv1[(g * 32 + T) * 4 + w] = il[2 * g + (w >> 1)][w & 1];
+            }
+    }
+}
+
+// ---------------------------------------------------------------- forward (CT), lazy: no corrections.
+// Input < B  ->  output < B + 2Q per stage; callers start below 2Q and end below 22Q < 2^32.
+HERDB_HD void fwd_pass1(u32 (&x)[32]) {           // strided layout, stages 0..4 (strides 512..32)
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+            u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[k + h]);
+            u32 u = x[k];
+            x[k] = u + v;
+            x[k + h] = u - v + kQ2;
+        }
+    }
+}
+HERDB_HD void fwd_pass2(u32 (&x)[32], const u32 (&tw)[62]) {   // contiguous layout, stages 5..9
+    int off = 0;
+#pragma unroll
+    for (int s = 5; s < 10; ++s) {
+        const int t = 16 >> (s - 5);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+            if (e & t) continue;
+            const int p = off + e / (2 * t);
+            u32 v = mul_shoup_lazy(tw[2 * p], tw[2 * p + 1], x[e + t]);
+            u32 u = x[e];
+            x[e] = u + v;
+            x[e + t] = u - v + kQ2;
+        }
+        off += 16 / t;
+    }
+}
+
+// ---------------------------------------------------------------- inverse (GS): invariant all values in [0, 2Q)
+HERDB_HD void inv_pass1(u32 (&x)[32], const u32* lane_tw /* smem or global, chunked [g][32][4] */, u32 lane) {
+    int off = 0;
+#pragma unroll
+    for (int t = 1; t <= 16; t <<= 1) {
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+            if (e & t) continue;
+            const int p = off + e / (2 * t);
+            const u32* tp = lane_tw + ((p >> 1) * 32 + lane) * 4 + (p & 1) * 2;
+            u32 u = x[e], v = x[e + t];
+            x[e] = csub(u + v, kQ2);
+            x[e + t] = mul_shoup_lazy(tp[0], tp[1], u - v + kQ2);
+        }
+        off += 16 / t;
+    }
+}
+HERDB_HD void inv_pass2(u32 (&x)[32]) {           // strided layout, strides 32..512
+#pragma unroll
+    for (int h = 1; h <= 16; h <<= 1) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = 16 / h + k / (2 * h);
+            u32 u = x[k], v = x[k + h];
+            x[k] = csub(u + v, kQ2);
+            x[k + h] = mul_shoup_lazy(HERDB_TWI(idx, 0), HERDB_TWI(idx, 1), u - v + kQ2);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- shared-memory movement (one polynomial = 1024 words)
+HERDB_HD void load_contig(const u32* poly, u32 lane, u32 (&x)[32]) {      // 8 x 128-bit, conflict free
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        V4 q = *reinterpret_cast<const V4*>(poly + 32 * lane + 4 * (c ^ (lane & 7)));
+        x[4 * c + 0] = q.v[0]; x[4 * c + 1] = q.v[1]; x[4 * c + 2] = q.v[2]; x[4 * c + 3] = q.v[3];
+    }
+}
+HERDB_HD void store_contig(u32* poly, u32 lane, const u32 (&x)[32]) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        V4 q;
+        q.v[0] = x[4 * c + 0]; q.v[1] = x[4 * c + 1]; q.v[2] = x[4 * c + 2]; q.v[3] = x[4 * c + 3];
+        *reinterpret_cast<V4*>(poly + 32 * lane + 4 * (c ^ (lane & 7))) = q;
+    }
+}
+HERDB_HD void load_strided(const u32* poly, u32 lane, u32 (&x)[32]) {     // 32 x 32-bit, conflict free
+#pragma unroll
+    for (int k = 0; k < 32; ++k) x[k] = poly[32 * k + ((((lane >> 2) ^ (k & 7)) << 2) | (lane & 3))];
+}
+HERDB_HD void store_strided(u32* poly, u32 lane, const u32 (&x)[32]) {
+#pragma unroll
+    for (int k = 0; k < 32; ++k) poly[32 * k + ((((lane >> 2) ^ (k & 7)) << 2) | (lane & 3))] = x[k];
+}
+
+}  // namespace herdb

@@ -1,0 +1,71 @@
+// CPU emulation of the blind-rotation CTA body (herdsman_b200/csrc/br_core.cuh): the very
+// same source the CUDA kernel compiles, run by 256 host threads with pthread barriers in
+// place of __syncthreads/__syncwarp.  TEST ONLY -- lets the indexing, swizzles, lazy
+// ranges and table layouts be checked against the oracle without a GPU.
+#include <pthread.h>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "../../herdsman_b200/csrc/br_core.cuh"
+#include "../../herdsman_b200/csrc/host_tables.h"
+
+using namespace herdb;
+
+struct HostEnv {
+    u32 tid_;
+    pthread_barrier_t* cta;
+    pthread_barrier_t* warps;
+    u32 tid() const { return tid_; }
+    void sync() { pthread_barrier_wait(cta); }
+    void syncwarp() { pthread_barrier_wait(&warps[tid_ >> 5]); }
+    V4 ldg_v4(const u32* p) const { return *reinterpret_cast<const V4*>(p); }
+};
+
+struct ThreadArg { HostEnv env; const BrParams* P; BrSmem* S; u32 groups; };
+
+static void* thread_main(void* a) {
+    ThreadArg* t = (ThreadArg*)a;
+    for (u32 g = 0; g < t->groups; ++g) blind_rotate_group(t->env, *t->P, *t->S, g);
+    return nullptr;
+}
+
+extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
+                                u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
+    const herdb_key_header* h = (const herdb_key_header*)blob;
+    if (len < sizeof *h || h->magic != HERDB_KEY_MAGIC) return -1;
+    const u32 n = h->n;
+    // bootstrapping key -> kernel NTT convention, scaled by 1/N
+    size_t polys = (size_t)n * 2 * kDG2 * 2;
+    std::vector<u32> bsk(polys * kN);
+    memcpy(bsk.data(), (const uint8_t*)blob + sizeof *h, bsk.size() * 4);
+    for (size_t p = 0; p < polys; ++p) {
+        ntt_forward_host(&bsk[p * kN]);
+        for (u32 x = 0; x < kN; ++x) bsk[p * kN + x] = cmulmod(bsk[p * kN + x], kNInv);
+    }
+    std::vector<u32> mono; build_monomial_table(mono);
+    std::vector<u32> ftw2(kLaneTwWords), itw1(kLaneTwWords);
+    build_lane_twiddles(ftw2.data(), itw1.data());
+    GateDesc gd{}; gd.gate = (uint8_t)gate; gd.pool_a = 0; gd.pool_b = 1; gd.pool_out = 2;
+    BrParams P{};
+    P.bsk = bsk.data(); P.mono = mono.data(); P.ftw2 = ftw2.data(); P.itw1 = itw1.data(); P.gates = &gd;
+    P.pools[0] = Pool{const_cast<u16*>(ct_a), 1, 0};
+    P.pools[1] = Pool{const_cast<u16*>(ct_b), 1, 0};
+    std::vector<u16> ext((size_t)batch * kExtStride);
+    P.ext = ext.data(); P.trace = trace_out; P.n = n; P.steps = steps; P.rows = batch; P.jobs = batch;
+    BrSmem* S = new BrSmem;
+    pthread_barrier_t cta, warps[8];
+    pthread_barrier_init(&cta, nullptr, kThreads);
+    for (auto& w : warps) pthread_barrier_init(&w, nullptr, 32);
+    std::vector<ThreadArg> args(kThreads);
+    std::vector<pthread_t> th(kThreads);
+    u32 groups = (batch + kC - 1) / kC;
+    pthread_attr_t attr; pthread_attr_init(&attr); pthread_attr_setstacksize(&attr, 1 << 20);
+    for (u32 t = 0; t < (u32)kThreads; ++t) {
+        args[t] = ThreadArg{HostEnv{t, &cta, warps}, &P, S, groups};
+        pthread_create(&th[t], &attr, thread_main, &args[t]);
+    }
+    for (auto& t : th) pthread_join(t, nullptr);
+    for (u32 b = 0; b < batch; ++b) memcpy(ext_out + (size_t)b * (kN + 1), &ext[(size_t)b * kExtStride], (kN + 1) * 2);
+    delete S;
+    return 0;
+}

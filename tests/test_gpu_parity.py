@@ -1,0 +1,143 @@
+"""GPU parity tests: the CUDA path (through the C ABI of include/herdb.h) against the CPU oracle on
+the same seeded keys and ciphertexts.  Bar: BIT-EXACT ciphertext equality (integer work)."""
+import numpy as np
+import pytest
+
+from herdsman_b200 import api, circuit as cm
+
+pytestmark = pytest.mark.gpu
+
+GATES = ["OR", "AND", "NOR", "NAND", "XOR_FAST", "XNOR_FAST"]
+PLAIN = {"OR": lambda a, b: a | b, "AND": lambda a, b: a & b, "NOR": lambda a, b: 1 - (a | b),
+         "NAND": lambda a, b: 1 - (a & b), "XOR_FAST": lambda a, b: a ^ b, "XNOR_FAST": lambda a, b: 1 - (a ^ b)}
+
+
+@pytest.fixture(scope="module")
+def backend():
+    b = api.Backend(devices=(0,))
+    yield b
+    b.close()
+
+
+@pytest.fixture(scope="module")
+def test_session(backend, test_key, oracle_lib):
+    backend.load_key_mem("test", test_key["blob"])
+    return {"name": "test", "oracle": oracle_lib.Oracle(test_key["blob"]), **test_key}
+
+
+@pytest.fixture(scope="module")
+def std_session(backend, std128_key, oracle_lib):
+    backend.load_key_mem("std128", std128_key["blob"])
+    return {"name": "std128", "oracle": oracle_lib.Oracle(std128_key["blob"]), **std128_key}
+
+
+def _inputs(sess, batch, seed):
+    rng = np.random.default_rng(seed)
+    a = rng.integers(0, 2, batch).astype(np.uint8); b = rng.integers(0, 2, batch).astype(np.uint8)
+    ca = api.client_encrypt_bits(sess["n"], sess["sk"], a, seed=seed, first=0)
+    cb = api.client_encrypt_bits(sess["n"], sess["sk"], b, seed=seed, first=1 << 20)
+    return a, b, ca, cb
+
+
+@pytest.mark.parametrize("gate", GATES)
+def test_gate_bit_exact_test_params(backend, test_session, gate):
+    s = test_session
+    a, b, ca, cb = _inputs(s, 37, seed=11)          # 37: ragged last group of 4
+    out = backend.eval_gate_batch(s["name"], gate, ca, cb)
+    ref = s["oracle"].gate(gate, ca, cb)
+    assert np.array_equal(out, ref)
+    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), PLAIN[gate](a, b))
+
+
+@pytest.mark.parametrize("batch", [1, 2, 3, 4, 5, 592, 593, 1200])
+def test_gate_batch_sizes(backend, test_session, batch):
+    s = test_session
+    a, b, ca, cb = _inputs(s, batch, seed=batch)
+    out = backend.eval_gate_batch(s["name"], "NAND", ca, cb)
+    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
+    k = min(batch, 24)
+    assert np.array_equal(out[:k], s["oracle"].gate("NAND", ca[:k], cb[:k]))
+    assert np.array_equal(out[-k:], s["oracle"].gate("NAND", ca[-k:], cb[-k:]))
+
+
+def test_gate_empty_batch(backend, test_session):
+    s = test_session
+    z = np.zeros((0, s["n"] + 1), np.uint16)
+    assert backend.eval_gate_batch(s["name"], "AND", z, z).shape == (0, s["n"] + 1)
+
+
+def test_gate_bit_exact_std128(backend, std_session):
+    s = std_session
+    a, b, ca, cb = _inputs(s, 24, seed=5)
+    for gate in ["NAND", "AND", "OR"]:
+        out = backend.eval_gate_batch(s["name"], gate, ca, cb)
+        ref = s["oracle"].gate(gate, ca, cb)
+        assert np.array_equal(out, ref), gate
+        assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), PLAIN[gate](a, b))
+
+
+def test_std128_large_batch_decrypts(backend, std_session):
+    """size-independent property at a larger size: every output decrypts to NAND of the inputs and
+    a bootstrapped output can feed another gate (noise is refreshed)"""
+    s = std_session
+    a, b, ca, cb = _inputs(s, 2048, seed=9)
+    out = backend.eval_gate_batch(s["name"], "NAND", ca, cb)
+    d1 = api.client_decrypt_bits(s["n"], s["sk"], out)
+    assert np.array_equal(d1, 1 - (a & b))
+    out2 = backend.eval_gate_batch(s["name"], "OR", out, ca)
+    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out2), d1 | a)
+
+
+@pytest.mark.parametrize("name,build,bits_in,plain", [
+    ("add8", lambda: cm.adder_circuit(8), (8, 8), lambda x, y: (x + y) % 256),
+    ("add8_model", lambda: cm.adder_circuit(8, "model"), (8, 8), lambda x, y: (x + y) % 256),
+    ("lt8", lambda: cm.compare_circuit(8), (8, 8), lambda x, y: (x < y).astype(np.uint64)),
+    ("mul8", lambda: cm.multiply_circuit(8), (8, 8), lambda x, y: (x * y) % 256),
+])
+def test_circuit_bit_exact_test_params(backend, test_session, name, build, bits_in, plain):
+    s = test_session
+    c = build()
+    rows = 9
+    rng = np.random.default_rng(3)
+    x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
+    bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
+    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=21)
+    out = backend.eval_circuit_rows(s["name"], c, rows_in)
+    dec = api.client_decrypt_bits(s["n"], s["sk"], out)
+    assert np.array_equal(cm.unpack_words(dec), plain(x, y))
+    ref = s["oracle"].circuit_rows(c.to_c(), rows_in, c.out_bits)
+    assert np.array_equal(out, ref)
+
+
+def test_circuit_constants_and_not_outputs(backend, test_session):
+    """outputs fed directly by NOT / constants / inputs (no bootstrap on the way)"""
+    s = test_session
+    c = cm.Circuit([[cm.DataType.BIT, cm.DataType.BIT]], [("o", cm.DataType.UINT8)])
+    a, b = c.input(0, 0, 0), c.input(0, 1, 0)
+    one, zero = c.constant(1), c.constant(0)
+    c.output_bit(0, 0, a); c.output_bit(0, 1, c.not_(a)); c.output_bit(0, 2, one); c.output_bit(0, 3, c.not_(one))
+    c.output_bit(0, 4, c.and_(a, one)); c.output_bit(0, 5, c.or_(c.not_(b), zero)); c.output_bit(0, 6, c.nand(a, b))
+    c.output_bit(0, 7, c.mux(a, b, c.not_(b)))
+    bits = np.array([[0, 0], [0, 1], [1, 0], [1, 1]], np.uint8)
+    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=33)
+    out = backend.eval_circuit_rows(s["name"], c, rows_in)
+    ref = s["oracle"].circuit_rows(c.to_c(), rows_in, 8)
+    assert np.array_equal(out, ref)
+    dec = api.client_decrypt_bits(s["n"], s["sk"], out)
+    A, B = bits[:, 0], bits[:, 1]
+    want = np.stack([A, 1 - A, np.ones(4, int), np.zeros(4, int), A, 1 - B, 1 - (A & B), np.where(A == 1, B, 1 - B)], axis=1)
+    assert np.array_equal(dec, want)
+
+
+def test_add8_std128_rows(backend, std_session):
+    s = std_session
+    c = cm.adder_circuit(8)
+    rows = 64
+    rng = np.random.default_rng(1)
+    x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
+    bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
+    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=1)
+    out = backend.eval_circuit_rows(s["name"], c, rows_in)
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out)), (x + y) % 256)
+    ref = s["oracle"].circuit_rows(c.to_c(), rows_in[:4], c.out_bits)      # oracle: ~7 s per row per core
+    assert np.array_equal(out[:4], ref)
