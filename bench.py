@@ -1,0 +1,274 @@
+#!/usr/bin/env python3
+"""bench.py -- bootstrapped binary gates per second (BASELINE.json metric).
+
+Workload (config.workload): BASELINE.json configs[1], the single-gate bootstrap microbench:
+one step = one batch of NAND gates on fresh STD128 (n=512, N=1024, Q=2^27-2^11+1) LWE
+ciphertexts per GPU, evaluated by the CUDA backend through the C ABI (include/herdb.h).
+
+  value  whole-job gates/s with the input ciphertexts resident in HBM (herdb_eval_gate_batch_dev)
+  e2e    the same through the host-buffer entry point (herdb_eval_gate_batch): H2D of the inputs
+         from pinned host memory + evaluation + D2H of the outputs inside the timed region
+  roofline / cpu_baseline / clocks / gpu_launches: see DESIGN.md "Measurement"
+
+  python bench.py --gpus 1 --steps 10 --warmup 3            (default)
+  torchrun --nproc-per-node N ... bench.py --gpus N ...      (one rank per GPU, rows/gates sharded,
+                                                              key blob broadcast once over NCCL)
+  python bench.py --impl reference ...                        (CPU arm: the oracle restating OpenFHE
+                                                              binfhe on all host threads)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_LWE = 512
+SEED = 0x48455244
+# algorithmic work per bootstrapped gate (SURVEY.md 8d / BASELINE.md 3)
+MODMUL_PER_GATE = 46_137_344
+# IMAD-pipe issue slots per gate of the algorithm itself: per CMUX step 51,200 Shoup
+# butterflies x 4 slots (IMAD.HI = 2, IMAD, IMAD) + 32,768 key MACs x 2 (IMAD.WIDE) + 4,096 monomial
+# products x 2; reductions of the 64-bit sums are overhead and not counted
+IMAD_SLOTS_PER_GATE = N_LWE * (51_200 * 4 + 32_768 * 2 + 4_096 * 2)
+BSK_BYTES = N_LWE * 2 * 8 * 2 * 1024 * 4
+KS_BYTES_PER_GATE = 1024 * 2 * (N_LWE + 1) * 2
+CT_BYTES = (N_LWE + 1) * 2
+
+
+def clocks_sampler(stop, out, gpu_index):
+    q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    while not stop.is_set():
+        try:
+            r = subprocess.run(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                               capture_output=True, text=True, timeout=5)
+            f = [x.strip() for x in r.stdout.strip().split(",")]
+            if len(f) >= 7:
+                out.append(f)
+        except Exception:
+            pass
+        stop.wait(0.2)
+
+
+def summarize_clocks(samples):
+    if not samples:
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    sm = sorted(float(s[0]) for s in samples)
+    reasons = []
+    for i, name in [(3, "hw_slowdown"), (4, "hw_thermal_slowdown"), (5, "sw_thermal_slowdown"), (6, "sw_power_cap")]:
+        if any(s[i].lower().startswith("active") for s in samples):
+            reasons.append(name)
+    return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(samples[0][1]), "reasons": reasons, "samples": len(samples)}
+
+
+def run_reference(args, rank, world):
+    """CPU arm: the oracle (port of OpenFHE binfhe gate evaluation) on all host threads."""
+    if rank != 0:
+        return
+    from oracle import pyoracle as po
+    cores = os.cpu_count() or 1
+    sk, skr, blob = po.keygen(N_LWE, SEED)
+    orc = po.Oracle(blob)
+    per_step = max(cores, args.ref_gates if args.ref_gates else 2 * cores)
+    rng = np.random.default_rng(2)
+    bits_a = rng.integers(0, 2, per_step).astype(np.uint8); bits_b = rng.integers(0, 2, per_step).astype(np.uint8)
+    ca = po.encrypt_bits(N_LWE, sk, bits_a, seed=2, first=0); cb = po.encrypt_bits(N_LWE, sk, bits_b, seed=2, first=1 << 24)
+    for _ in range(args.warmup):
+        orc.gate("NAND", ca[:cores], cb[:cores], threads=cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = orc.gate("NAND", ca, cb, threads=cores)
+    dt = time.perf_counter() - t0
+    assert np.array_equal(po.decrypt_bits(N_LWE, sk, out), 1 - (bits_a & bits_b))
+    v = per_step * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "bootstrapped binary gates/sec", "value": v, "unit": "gates/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32 (u64 products)", "data": "synthetic",
+        "config": {"workload": "configs[1]: single-gate NAND bootstrap, STD128 (n=512,N=1024,Q=134215681,baseG=128,qKS=2^14,baseKS=128)",
+                   "gates_per_step": per_step, "note": "reference CPU path = oracle/ restating OpenFHE binfhe v1.0.x; OpenFHE itself is not in the reference tree"},
+        "cpu_baseline": {"value": v, "unit": "gates/s", "cores": cores, "kind": "port",
+                         "sample": "%d NAND gates per step x %d steps, OpenMP over gates" % (per_step, args.steps)},
+        "e2e": {"value": v, "unit": "gates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    from herdsman_b200 import api
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    be = api.Backend(devices=(local_rank,))          # raises without a CUDA device: no CPU fallback
+
+    # ---- keys: generated once (client stand-in) on rank 0, broadcast over NVLink (NCCL), converted on each GPU
+    blob_size = api.lib().herdb_client_key_blob_size(N_LWE)
+    sk = np.zeros(N_LWE, np.int8)
+    if rank == 0:
+        sk, skr, blob = api.client_keygen(N_LWE, SEED)
+        d_blob = torch.from_numpy(blob).to(dev)
+    else:
+        d_blob = torch.empty(blob_size, dtype=torch.uint8, device=dev)
+    if world > 1:
+        dist.broadcast(d_blob, src=0)
+        t_sk = torch.from_numpy(sk.copy()).to(dev); dist.broadcast(t_sk, src=0); sk = t_sk.cpu().numpy()
+    torch.cuda.synchronize()
+    be.load_key_dev("bench", d_blob, blob_size)
+    del d_blob
+    torch.cuda.empty_cache()
+
+    # ---- synthetic encrypted inputs (per rank), pinned on the host and resident in HBM
+    B = args.batch
+    w = N_LWE + 1
+    rng = np.random.default_rng(100 + rank)
+    bits_a = rng.integers(0, 2, B).astype(np.uint8); bits_b = rng.integers(0, 2, B).astype(np.uint8)
+    h_a = torch.empty((B, w), dtype=torch.uint16, pin_memory=True); h_b = torch.empty_like(h_a).pin_memory()
+    h_out = torch.empty((B, w), dtype=torch.uint16, pin_memory=True)
+    api.client_encrypt_bits(N_LWE, sk, bits_a, seed=2 + rank, first=0, out=h_a.numpy())
+    api.client_encrypt_bits(N_LWE, sk, bits_b, seed=2 + rank, first=1 << 24, out=h_b.numpy())
+    d_a = h_a.to(dev); d_b = h_b.to(dev); d_out = torch.zeros((B, w), dtype=torch.uint16, device=dev)
+    ext = torch.cuda.ExternalStream(be.stream(), device=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(ext)
+        for _ in range(steps):
+            fn()
+        e1.record(ext)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        barrier()
+        if dist is not None:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    dev_step = lambda: be.eval_gate_batch_dev("bench", "NAND", d_a, d_b, d_out, B)
+    e2e_step = lambda: be.eval_gate_batch("bench", "NAND", h_a, h_b, h_out)
+
+    peaks = be.measure_int_peak() if rank == 0 else {}
+    for _ in range(max(3, args.warmup)):
+        dev_step()
+    stop = threading.Event(); samples = []
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples, local_rank), daemon=True); th.start()
+    be.reset_stats()
+    ms = timed(dev_step, args.steps)
+    st = be.stats()
+    stop.set(); th.join()
+    clocks = summarize_clocks(samples)
+    for _ in range(2):
+        e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+
+    # correctness of what was timed: every output decrypts to NAND of the inputs
+    ok_dev = np.array_equal(api.client_decrypt_bits(N_LWE, sk, d_out.cpu().numpy()), 1 - (bits_a & bits_b))
+    ok_e2e = np.array_equal(api.client_decrypt_bits(N_LWE, sk, h_out.numpy()), 1 - (bits_a & bits_b))
+    if not (ok_dev and ok_e2e):
+        raise SystemExit("bench: decrypted outputs do not match NAND of the inputs")
+    if rank != 0:
+        return
+
+    gates = world * B * args.steps
+    value = gates / (ms * 1e-3)
+    e2e_value = gates / (ms_e2e * 1e-3)
+    br_ms = st["blind_rotate_ms"] / max(1, st["blind_rotate_launches"])
+    ks_ms = st["keyswitch_ms"] / max(1, st["keyswitch_launches"])
+    jobs_per_launch = st["gates_bootstrapped"] / max(1, st["blind_rotate_launches"])
+    imad_peak = peaks.get("imad_tops") or 18.4
+    achieved_slots = jobs_per_launch * IMAD_SLOTS_PER_GATE / (br_ms * 1e-3) / 1e12
+    try:
+        hbm_peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]; peak_src = "measured"
+    except Exception:
+        hbm_peak = 6650.0; peak_src = "fallback"
+    br_bytes = jobs_per_launch * (2 * CT_BYTES + 2 * 1025) + BSK_BYTES      # BSK streamed once per launch (R = jobs/launch)
+    ks_bytes = jobs_per_launch * (KS_BYTES_PER_GATE + 2 * 1025 + CT_BYTES)
+    line = {
+        "metric": "bootstrapped binary gates/sec", "value": value, "unit": "gates/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32 (u64 products)", "data": "synthetic",
+        "config": {"workload": "configs[1]: single-gate NAND bootstrap, STD128 (n=512,N=1024,Q=134215681,baseG=128,qKS=2^14,baseKS=128)",
+                   "gates_per_step_per_gpu": B, "parallelism": "gates sharded over %d GPU(s), no data-path collective; key blob NCCL-broadcast once" % world,
+                   "l2": "working set per step (BSK 64 MiB + KSK 260 MiB + monomials 4 MiB + %.0f MiB ciphertexts) exceeds the 126 MB L2" % (B * (3 * CT_BYTES + 2064) / 2**20)},
+        "e2e": {"value": e2e_value, "unit": "gates/s", "h2d_bytes_per_step": 2 * B * CT_BYTES * world, "d2h_bytes_per_step": B * CT_BYTES * world,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": int(st["kernel_launches"]) * world,
+        "clocks": clocks,
+        "roofline": {"bound": "int32-imad", "kernel": "blind_rotate_kernel", "achieved": achieved_slots, "peak": imad_peak,
+                     "unit": "T IMAD-slots/s", "frac": achieved_slots / imad_peak, "peak_source": "measured in this run (herdb_measure_int_peak)",
+                     "traffic": None, "modmul_per_s": jobs_per_launch * MODMUL_PER_GATE / (br_ms * 1e-3),
+                     "kernel_ms": br_ms, "jobs_per_launch": jobs_per_launch, "share_of_step": st["blind_rotate_ms"] / ms,
+                     "int_peaks_tops": peaks,
+                     "hbm": {"bound": "hbm", "achieved": br_bytes / (br_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": br_bytes / (br_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": peak_src,
+                             "keyswitch_kernel": {"achieved": ks_bytes / (ks_ms * 1e-3) / 1e9 if ks_ms else None, "kernel_ms": ks_ms,
+                                                  "frac": (ks_bytes / (ks_ms * 1e-3) / 1e9 / hbm_peak) if ks_ms else None}}},
+        "kernels": {"blind_rotate_ms": br_ms, "keyswitch_ms": ks_ms},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(be, sk, args)
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(be, sk, args):
+    """oracle (port of OpenFHE binfhe EvalBinGate) on the box's host cores, bounded sample; also the parity check"""
+    from herdsman_b200 import api
+    from oracle import pyoracle as po
+    cores = os.cpu_count() or 1
+    _, _, blob = api.client_keygen(N_LWE, SEED)
+    orc = po.Oracle(blob)
+    cnt = cores * args.cpu_gates_per_core
+    rng = np.random.default_rng(7)
+    a = rng.integers(0, 2, cnt).astype(np.uint8); b = rng.integers(0, 2, cnt).astype(np.uint8)
+    ca = api.client_encrypt_bits(N_LWE, sk, a, seed=77, first=0); cb = api.client_encrypt_bits(N_LWE, sk, b, seed=77, first=1 << 24)
+    orc.gate("NAND", ca[:cores], cb[:cores], threads=cores)
+    t0 = time.perf_counter()
+    ref = orc.gate("NAND", ca, cb, threads=cores)
+    dt = time.perf_counter() - t0
+    got = be.eval_gate_batch("bench", "NAND", ca, cb)
+    return {"value": cnt / dt, "unit": "gates/s", "cores": cores, "kind": "port",
+            "sample": "%d NAND gates (same keys, STD128), OpenMP over gates, %.1f s" % (cnt, dt),
+            "parity": "GPU == oracle bit-exact on %d/%d sampled gates" % (int((got == ref).all(axis=1).sum()), cnt)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=32768, help="gates per step per GPU")
+    ap.add_argument("--ref-gates", type=int, default=0, help="reference arm: gates per step (default 2 x cores)")
+    ap.add_argument("--cpu-gates-per-core", type=int, default=48)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

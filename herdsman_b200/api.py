@@ -31,7 +31,7 @@ EXPORTS = [
     "herdb_load_key", "herdb_load_key_mem", "herdb_load_key_dev", "herdb_unload_key", "herdb_key_lwe_n",
     "herdb_map_async", "herdb_wait_idle",
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
-    "herdb_circuit_analyze", "herdb_get_stats", "herdb_reset_stats", "herdb_measure_int_peak",
+    "herdb_circuit_analyze", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_client_key_blob_size", "herdb_client_keygen", "herdb_client_encrypt_bits", "herdb_client_decrypt_bits",
 ]
 
@@ -80,6 +80,7 @@ def lib():
         L.herdb_eval_circuit_rows_dev.argtypes = [vp, cp, ci, C.POINTER(herdb_circuit), vp, vp, sz]
         L.herdb_circuit_analyze.argtypes = [C.POINTER(herdb_circuit), C.POINTER(herdb_circuit_info)]
         L.herdb_get_stats.argtypes = [vp, ci, C.POINTER(herdb_stats)]
+        L.herdb_get_stream.argtypes = [vp, ci, C.POINTER(vp)]
         L.herdb_reset_stats.argtypes = [vp]
         L.herdb_measure_int_peak.argtypes = [vp, ci] + [C.POINTER(C.c_double)] * 5
         L.herdb_client_key_blob_size.argtypes = [u32]; L.herdb_client_key_blob_size.restype = sz
@@ -221,6 +222,12 @@ class Backend:
         s = herdb_stats()
         self._check(self.L.herdb_get_stats(self.h, device, C.byref(s)))
         return {k: getattr(s, k) for k, _ in herdb_stats._fields_}
+
+    def stream(self, device=0):
+        """raw cudaStream_t of the device's launch stream (wrap with torch.cuda.ExternalStream)"""
+        p = C.c_void_p()
+        self._check(self.L.herdb_get_stream(self.h, device, C.byref(p)))
+        return p.value
 
     def reset_stats(self):
         self._check(self.L.herdb_reset_stats(self.h))

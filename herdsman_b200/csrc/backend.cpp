@@ -474,6 +474,11 @@ extern "C" int herdb_get_stats(herdb_ctx* ctx, int device, herdb_stats* out) {
     *out = ctx->devs[device]->stats;
     return HERDB_OK;
 }
+extern "C" int herdb_get_stream(herdb_ctx* ctx, int device, void** stream_out) {
+    if (!ctx || !stream_out || device < 0 || device >= (int)ctx->devs.size()) return HERDB_ERR_ARG;
+    *stream_out = (void*)ctx->devs[device]->stream;
+    return HERDB_OK;
+}
 extern "C" int herdb_reset_stats(herdb_ctx* ctx) {
     if (!ctx) return HERDB_ERR_ARG;
     for (Device* d : ctx->devs) { std::lock_guard<std::mutex> l(d->mu); d->stats = herdb_stats{}; }

@@ -172,6 +172,9 @@ typedef struct herdb_stats {
     uint64_t h2d_bytes, d2h_bytes;
 } herdb_stats;
 int herdb_get_stats(herdb_ctx* ctx, int device, herdb_stats* out);
+/* the cudaStream_t (as void*) every kernel and copy of ctx device `device` is enqueued on, so a
+ * caller can bracket work with its own CUDA events on the launching stream */
+int herdb_get_stream(herdb_ctx* ctx, int device, void** stream_out);
 int herdb_reset_stats(herdb_ctx* ctx);
 /* raw integer-pipe peak microbenchmark (IMAD / IADD3 / IMAD.HI / IMAD.WIDE), Tops/s */
 int herdb_measure_int_peak(herdb_ctx* ctx, int device, double* imad_tops, double* iadd3_tops,
