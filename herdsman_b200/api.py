@@ -29,7 +29,7 @@ GATE = {"OR": 0, "AND": 1, "NOR": 2, "NAND": 3, "XOR_FAST": 4, "XNOR_FAST": 5}
 EXPORTS = [
     "herdb_create", "herdb_destroy", "herdb_strerror", "herdb_last_error", "herdb_device_count",
     "herdb_load_key", "herdb_load_key_mem", "herdb_load_key_dev", "herdb_unload_key", "herdb_key_lwe_n",
-    "herdb_map_async", "herdb_wait_idle",
+    "herdb_map_async", "herdb_wait_idle", "herdb_partition_read", "herdb_partition_write", "herdb_partition_rows",
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_client_key_blob_size", "herdb_client_keygen", "herdb_client_encrypt_bits", "herdb_client_decrypt_bits",
@@ -74,6 +74,9 @@ def lib():
         L.herdb_key_lwe_n.argtypes = [vp, cp, C.POINTER(u32)]
         L.herdb_map_async.argtypes = [vp, cp, cp, u32, u64, cp, u32, C.POINTER(herdb_circuit), DONE_FN, vp]
         L.herdb_wait_idle.argtypes = [vp]
+        L.herdb_partition_read.argtypes = [cp, u64, sz, vp]
+        L.herdb_partition_write.argtypes = [cp, u64, sz, vp]
+        L.herdb_partition_rows.argtypes = [u64, u32, u32]; L.herdb_partition_rows.restype = u64
         L.herdb_eval_gate_batch.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz]
         L.herdb_eval_gate_batch_dev.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz]
         L.herdb_eval_circuit_rows.argtypes = [vp, cp, C.POINTER(herdb_circuit), vp, vp, sz]
@@ -110,6 +113,29 @@ def analyze(circuit: Circuit):
     if rc:
         raise HerdbError(rc)
     return {k: getattr(info, k) for k, _ in herdb_circuit_info._fields_}
+
+
+# ------------------------------------------------------------------------------------------------ partition files
+def partition_write(path, rows):
+    """rows: uint16 array [n_rows, bits, n+1] (or [n_rows, words]); framing [u32 len][payload] per row"""
+    rows = np.ascontiguousarray(rows, np.uint16)
+    n_rows = rows.shape[0]
+    row_bytes = (rows.size // n_rows) * 2 if n_rows else 0
+    rc = lib().herdb_partition_write(str(path).encode(), n_rows, row_bytes, _ptr(rows) if rows.size else None)
+    if rc:
+        raise HerdbError(rc, str(path))
+
+
+def partition_read(path, n_rows, bits, n):
+    out = np.zeros((n_rows, bits, n + 1), np.uint16)
+    rc = lib().herdb_partition_read(str(path).encode(), n_rows, bits * (n + 1) * 2, _ptr(out) if out.size else None)
+    if rc:
+        raise HerdbError(rc, str(path))
+    return out
+
+
+def partition_rows(rows, partitions, k):
+    return lib().herdb_partition_rows(rows, partitions, k)
 
 
 # ------------------------------------------------------------------------------------------------ client stand-in

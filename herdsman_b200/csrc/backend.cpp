@@ -527,34 +527,17 @@ std::string partition_path(const herdb_ctx* ctx, const std::string& session, con
 }
 
 int read_partition(herdb_ctx* ctx, const std::string& path, uint64_t row_count, size_t row_bytes, std::vector<uint16_t>& rows) {
-    FILE* f = fopen(path.c_str(), "rb");
-    if (!f) { ctx->set_error("cannot open partition " + path); return HERDB_ERR_IO; }
     rows.resize(row_count * row_bytes / 2);
-    for (uint64_t r = 0; r < row_count; ++r) {
-        uint32_t len = 0;
-        if (fread(&len, sizeof len, 1, f) != 1) { fclose(f); ctx->set_error("partition " + path + ": fewer rows than row_count"); return HERDB_ERR_FORMAT; }
-        if (len != row_bytes) { fclose(f); ctx->set_error("partition " + path + ": row length does not match the circuit inputs"); return HERDB_ERR_FORMAT; }
-        if (row_bytes && fread(reinterpret_cast<uint8_t*>(rows.data()) + r * row_bytes, row_bytes, 1, f) != 1) {
-            fclose(f); ctx->set_error("partition " + path + ": truncated row"); return HERDB_ERR_FORMAT;
-        }
-    }
-    fclose(f);
-    return HERDB_OK;
+    const int rc = herdb_partition_read(path.c_str(), row_count, row_bytes, rows.data());
+    if (rc == HERDB_ERR_IO) ctx->set_error("cannot open partition " + path);
+    else if (rc) ctx->set_error("partition " + path + ": row count / row length does not match the task (row_count, circuit inputs)");
+    return rc;
 }
 
 int write_partition(herdb_ctx* ctx, const std::string& path, uint64_t row_count, size_t row_bytes, const std::vector<uint16_t>& rows) {
-    const std::string tmp = path + ".tmp";
-    FILE* f = fopen(tmp.c_str(), "wb");
-    if (!f) { ctx->set_error("cannot create " + tmp); return HERDB_ERR_IO; }
-    const uint32_t len = (uint32_t)row_bytes;
-    bool ok = true;
-    for (uint64_t r = 0; r < row_count && ok; ++r) {
-        ok = fwrite(&len, sizeof len, 1, f) == 1;
-        if (ok && row_bytes) ok = fwrite(reinterpret_cast<const uint8_t*>(rows.data()) + r * row_bytes, row_bytes, 1, f) == 1;
-    }
-    ok = (fclose(f) == 0) && ok;
-    if (!ok || rename(tmp.c_str(), path.c_str()) != 0) { remove(tmp.c_str()); ctx->set_error("cannot write partition " + path); return HERDB_ERR_IO; }
-    return HERDB_OK;
+    const int rc = herdb_partition_write(path.c_str(), row_count, row_bytes, rows.data());
+    if (rc) ctx->set_error("cannot write partition " + path);
+    return rc;
 }
 
 int run_map_task(herdb_ctx* ctx, const MapTaskReq& t) {
@@ -579,6 +562,43 @@ int run_map_task(herdb_ctx* ctx, const MapTaskReq& t) {
 }
 
 }  // namespace
+
+extern "C" int herdb_partition_read(const char* path, uint64_t row_count, size_t row_bytes, void* rows_out) {
+    if (!path || (!rows_out && row_count && row_bytes)) return HERDB_ERR_ARG;
+    FILE* f = fopen(path, "rb");
+    if (!f) return HERDB_ERR_IO;
+    int rc = HERDB_OK;
+    for (uint64_t r = 0; r < row_count && !rc; ++r) {
+        uint32_t len = 0;
+        if (fread(&len, sizeof len, 1, f) != 1) rc = HERDB_ERR_FORMAT;                    // fewer rows than row_count
+        else if (len != row_bytes) rc = HERDB_ERR_FORMAT;                                 // ragged / foreign payload
+        else if (row_bytes && fread(static_cast<uint8_t*>(rows_out) + r * row_bytes, row_bytes, 1, f) != 1) rc = HERDB_ERR_FORMAT;
+    }
+    if (!rc && fgetc(f) != EOF) rc = HERDB_ERR_FORMAT;                                    // more rows than row_count
+    fclose(f);
+    return rc;
+}
+
+extern "C" int herdb_partition_write(const char* path, uint64_t row_count, size_t row_bytes, const void* rows) {
+    if (!path || (!rows && row_count && row_bytes) || row_bytes > 0xFFFFFFFFull) return HERDB_ERR_ARG;
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return HERDB_ERR_IO;
+    const uint32_t len = (uint32_t)row_bytes;
+    bool ok = true;
+    for (uint64_t r = 0; r < row_count && ok; ++r) {
+        ok = fwrite(&len, sizeof len, 1, f) == 1;
+        if (ok && row_bytes) ok = fwrite(static_cast<const uint8_t*>(rows) + r * row_bytes, row_bytes, 1, f) == 1;
+    }
+    ok = (fclose(f) == 0) && ok;
+    if (!ok || rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); return HERDB_ERR_IO; }
+    return HERDB_OK;
+}
+
+extern "C" uint64_t herdb_partition_rows(uint64_t rows, uint32_t partitions, uint32_t k) {
+    if (!partitions || k >= partitions) return 0;
+    return rows / partitions + (k < rows % partitions ? 1 : 0);
+}
 
 static void worker_loop(herdb_ctx* ctx) {
     for (;;) {

@@ -133,6 +133,16 @@ int herdb_map_async(herdb_ctx* ctx, const char* session_uuid,
                     const herdb_circuit* circuit, herdb_done_fn done, void* user);
 /* blocks until every task scheduled so far has completed */
 int herdb_wait_idle(herdb_ctx* ctx);
+/* Partition-file framing used by the task path (host only, no device needed):
+ * rows concatenated, each [u32 length, host endian][payload]  (storage_service.cpp:19-28,133-135).
+ * read: exactly `row_count` rows of exactly `row_bytes` payload each, else HERDB_ERR_FORMAT / _IO.
+ * write: to "<path>.tmp", then rename() so a partial file is never observed
+ * (lambda_http_worker_group.cpp:244-259 treats existence of the file as success). */
+int herdb_partition_read(const char* path, uint64_t row_count, size_t row_bytes, void* rows_out);
+int herdb_partition_write(const char* path, uint64_t row_count, size_t row_bytes, const void* rows);
+/* rows of partition k when `rows` rows are dealt to `partitions` files: rows/P + (k < rows%P)
+ * (storage_service.cpp:121-129,328-331) */
+uint64_t herdb_partition_rows(uint64_t rows, uint32_t partitions, uint32_t k);
 
 /* ------------------------------------------------------------------ file-less entry points
  * Host buffers (the end-to-end path: H2D + evaluate + D2H).

@@ -335,6 +335,15 @@ uint32_t orc_round_qQ_int(uint32_t v, uint32_t q, uint32_t Q) {
     return (uint32_t)(((2 * (uint64_t)v * q + Q) / (2 * (uint64_t)Q)) % q);
 }
 
+/* number of v in [start, start+count) where the double and the integer form differ (tests) */
+uint64_t orc_round_mismatches(uint32_t q, uint32_t Q, uint32_t start, uint32_t count) {
+    uint64_t bad = 0;
+    #pragma omp parallel for reduction(+:bad)
+    for (uint64_t v = start; v < (uint64_t)start + count; ++v)
+        bad += orc_round_qQ_double((uint32_t)v, q, Q) != orc_round_qQ_int((uint32_t)v, q, Q);
+    return bad;
+}
+
 /* RingGSWAccumulator::SignedDigitDecompose, VARIANT A, for one coefficient */
 void orc_signed_digit_decompose(uint32_t t, int32_t digits[DG]) {
     const int64_t Q_int = (int64_t)QQ;

@@ -56,6 +56,7 @@ void     orc_blind_rotate_trace(const orc_ctx*, int gate, const uint16_t* ct1, c
 void     orc_bootstrap_extract(const orc_ctx*, int gate, const uint16_t* ct1, const uint16_t* ct2, uint16_t* ext);
 uint32_t orc_round_qQ_double(uint32_t v, uint32_t q, uint32_t Q);    /* OpenFHE RoundqQ, double */
 uint32_t orc_round_qQ_int(uint32_t v, uint32_t q, uint32_t Q);       /* integer form used on GPU */
+uint64_t orc_round_mismatches(uint32_t q, uint32_t Q, uint32_t start, uint32_t count);
 void     orc_signed_digit_decompose(uint32_t t, int32_t digits[HERDB_DIGITS_G]);
 
 /* client side (what libherd does; synthetic) */

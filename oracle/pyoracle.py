@@ -47,6 +47,7 @@ def lib():
         L.orc_bootstrap_extract.argtypes = [vp, ci, vp, vp, vp]
         L.orc_round_qQ_double.argtypes = [u32, u32, u32]; L.orc_round_qQ_double.restype = u32
         L.orc_round_qQ_int.argtypes = [u32, u32, u32]; L.orc_round_qQ_int.restype = u32
+        L.orc_round_mismatches.argtypes = [u32, u32, u32, u32]; L.orc_round_mismatches.restype = u64
         L.orc_signed_digit_decompose.argtypes = [u32, vp]
         L.orc_key_blob_size.argtypes = [u32]; L.orc_key_blob_size.restype = sz
         L.orc_keygen.argtypes = [u32, u64, vp, vp, vp, sz]

@@ -1,0 +1,120 @@
+"""GPU tests of the drop-in seam: IWorkerGroup::schedule_task(MapTask) through herdb_map_async, with
+herdsman's on-disk layout -- <key_dir>/<session>/1.key and <storage_dir>/<session>/<df>/<partition>
+(key_service.cpp:28-31, storage_service.cpp:19-28) -- checked against the oracle's per-row interpreter."""
+import os
+import uuid
+
+import numpy as np
+import pytest
+
+from herdsman_b200 import api, circuit as cm
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def world(tmp_path_factory, test_key, oracle_lib):
+    root = tmp_path_factory.mktemp("herd")
+    key_dir, storage = root / "keys", root / "storage"
+    session = str(uuid.uuid4())
+    (key_dir / session).mkdir(parents=True)
+    (key_dir / session / "1.key").write_bytes(test_key["blob"].tobytes())        # SchemaType::BINFHE == 1
+    wg = api.CudaWorkerGroup(str(storage), str(key_dir), devices=(0,))
+    yield {"wg": wg, "session": session, "storage": storage, "oracle": oracle_lib.Oracle(test_key["blob"]), **test_key}
+    wg.close()
+
+
+def _frame(w, rows, parts):
+    """create_data_frame + append_to_data_frame: deal rows to partition files 0..P-1 in order"""
+    df = str(uuid.uuid4())
+    d = w["storage"] / w["session"] / df
+    d.mkdir(parents=True)
+    start = 0
+    for k in range(parts):
+        cnt = api.partition_rows(rows.shape[0], parts, k)
+        api.partition_write(d / str(k), rows[start:start + cnt])
+        start += cnt
+    return df
+
+
+def _task(w, c, in_df, out_df, part, rows):
+    return api.MapTask(w["session"], api.InputDataFramePtr(api.DataFramePtr(in_df, part), rows),
+                       api.DataFramePtr(out_df, part), api.CryptoKeyPtr(1), c)
+
+
+def test_map_tasks_over_partitions_match_oracle(world):
+    w = world
+    c = cm.adder_circuit(8)
+    n_rows, parts = 11, 3                                        # ragged: 4 + 4 + 3
+    rng = np.random.default_rng(0)
+    x = rng.integers(0, 256, n_rows); y = rng.integers(0, 256, n_rows)
+    bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
+    rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=40)
+    in_df = _frame(w, rows, parts)
+    out_df = str(uuid.uuid4())
+    (w["storage"] / w["session"] / out_df).mkdir(parents=True)   # ExecutionService creates the output frame dir
+    handles, seen = [], []
+    for k in range(parts):
+        h = w["wg"].schedule_task(_task(w, c, in_df, out_df, k, api.partition_rows(n_rows, parts, k)))
+        h.set_completion_callback(lambda st, k=k: seen.append((k, st)))           # installed AFTER scheduling (executor.cpp:86-93)
+        handles.append(h)
+    assert w["wg"].concurrent_workers() >= 1
+    for h in handles:
+        assert h.wait(300) == api.TaskHandle.Status.COMPLETED and h.completed()
+    assert sorted(seen) == [(k, api.TaskHandle.Status.COMPLETED) for k in range(parts)]
+    got = np.concatenate([api.partition_read(w["storage"] / w["session"] / out_df / str(k), api.partition_rows(n_rows, parts, k), 8, w["n"])
+                          for k in range(parts)])
+    assert not list((w["storage"] / w["session"] / out_df).glob("*.tmp"))
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got)), (x + y) % 256)
+    assert np.array_equal(got, w["oracle"].circuit_rows(c.to_c(), rows, 8))       # bit-exact with the per-row interpreter
+
+
+def test_chained_map_stages(world):
+    """config 5 shape: add -> compare -> select as three map tasks over intermediate frames on disk"""
+    w = world
+    n_rows = 5
+    rng = np.random.default_rng(1)
+    a = rng.integers(0, 256, n_rows); b = rng.integers(0, 256, n_rows); t = rng.integers(0, 256, n_rows)
+    D = cm.DataType
+    # stage 1: (a, b, t) -> (a+b, t)
+    s1 = cm.Circuit([[D.UINT8, D.UINT8, D.UINT8]], [("s", D.UINT8), ("t", D.UINT8)])
+    s1.output_word(0, cm._ripple_add(s1, s1.input_word(0, 0), s1.input_word(0, 1), "wire")); s1.output_word(1, s1.input_word(0, 2))
+    # stage 2: (s, t) -> (s < t, s, t)
+    s2 = cm.Circuit([[D.UINT8, D.UINT8]], [("lt", D.BIT), ("s", D.UINT8), ("t", D.UINT8)])
+    xs, ys = s2.input_word(0, 0), s2.input_word(0, 1)
+    s2.output_bit(0, 0, cm._less_than(s2, xs, ys, "wire")); s2.output_word(1, xs); s2.output_word(2, ys)
+    s3 = cm.select_circuit(8)
+    bits = np.concatenate([cm.pack_words(a, 8), cm.pack_words(b, 8), cm.pack_words(t, 8)], axis=1)
+    rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=41)
+    df = _frame(w, rows, 1)
+    ref = rows
+    for c in (s1, s2, s3):
+        out_df = str(uuid.uuid4()); (w["storage"] / w["session"] / out_df).mkdir(parents=True)
+        assert w["wg"].schedule_task(_task(w, c, df, out_df, 0, n_rows)).wait(300) == api.TaskHandle.Status.COMPLETED
+        ref = w["oracle"].circuit_rows(c.to_c(), ref, c.out_bits)
+        df = out_df
+    got = api.partition_read(w["storage"] / w["session"] / df / "0", n_rows, 8, w["n"])
+    assert np.array_equal(got, ref)
+    s = (a + b) % 256
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got)), np.where(s < t, s, t))
+
+
+def test_empty_partition_and_error_statuses(world):
+    w = world
+    c = cm.single_gate_circuit()
+    in_df = _frame(w, np.zeros((0, 2, w["n"] + 1), np.uint16), 1)
+    out_df = str(uuid.uuid4()); (w["storage"] / w["session"] / out_df).mkdir(parents=True)
+    assert w["wg"].schedule_task(_task(w, c, in_df, out_df, 0, 0)).wait(120) == api.TaskHandle.Status.COMPLETED
+    assert (w["storage"] / w["session"] / out_df / "0").read_bytes() == b""
+    # missing input partition, wrong row_count, wrong row payload size, unknown session key => ERROR (job fails, executor.cpp:168-178)
+    assert w["wg"].schedule_task(_task(w, c, in_df, out_df, 7, 1)).wait(120) == api.TaskHandle.Status.ERROR
+    assert w["wg"].schedule_task(_task(w, c, in_df, out_df, 0, 3)).wait(120) == api.TaskHandle.Status.ERROR
+    add = cm.adder_circuit(8)
+    rows = api.client_encrypt_bits(w["n"], w["sk"], np.zeros((2, 2), np.uint8), seed=42)
+    df2 = _frame(w, rows, 1)
+    assert w["wg"].schedule_task(_task(w, add, df2, out_df, 0, 2)).wait(120) == api.TaskHandle.Status.ERROR
+    bad = _task(w, c, df2, out_df, 0, 2); bad.session_uuid = str(uuid.uuid4())
+    assert w["wg"].schedule_task(bad).wait(120) == api.TaskHandle.Status.ERROR
+    # malformed circuit is refused at schedule time and reported through the handle
+    broken = cm.Circuit([[cm.DataType.BIT]], [("o", cm.DataType.BIT)]); broken.output_bit(0, 0, broken.input(0, 5, 0))
+    assert w["wg"].schedule_task(_task(w, broken, df2, out_df, 0, 2)).wait(120) == api.TaskHandle.Status.ERROR
