@@ -166,3 +166,21 @@ def test_task_handle_callback_semantics():
     assert seen == [api.TaskHandle.Status.COMPLETED] and h.completed()
     h2 = api.TaskHandle(); h2.set_completion_callback(seen.append); h2._mark_completed(api.TaskHandle.Status.ERROR)
     assert seen[-1] == api.TaskHandle.Status.ERROR
+
+
+def test_reference_side_adapter_compiles_against_herdsman_headers(tmp_path):
+    """include/herd_b200/cuda_worker_group.hpp is the binding a herdsman maintainer adds; where the
+    reference tree is present (build container only) it must compile against the real IWorkerGroup /
+    MapTask / Circuit headers (libuuid's header is absent here: a 2-line typedef shim stands in)."""
+    import subprocess
+    ref = "/root/reference"
+    if not os.path.isdir(os.path.join(ref, "include", "execution")):
+        pytest.skip("reference tree not present on this machine")
+    (tmp_path / "uuid").mkdir()
+    (tmp_path / "uuid" / "uuid.h").write_text("#pragma once\ntypedef unsigned char uuid_t[16];\n")
+    src = tmp_path / "check.cpp"
+    src.write_text('#include "herd_b200/cuda_worker_group.hpp"\nint main() { return sizeof(CudaWorkerGroup) > 0 ? 0 : 1; }\n')
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    r = subprocess.run([cxx, "-std=c++20", "-fsyntax-only", "-Wall", "-I", str(tmp_path), "-I", ref + "/include",
+                        "-I", ref + "/common/include", "-I", os.path.join(ROOT, "include"), str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
