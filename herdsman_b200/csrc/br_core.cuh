@@ -25,8 +25,15 @@
 
 namespace herdb {
 
-constexpr int kC = 4;                       // ciphertexts per CTA
-constexpr int kThreads = 256;               // 8 warps = kC * 2 polynomials
+// ciphertexts per CTA is a template parameter C (2 or 4); a CTA has 64*C threads = 2*C warps, one
+// warp per (ciphertext, component) polynomial in phase A, 16/C evaluation points per thread in phase B
+constexpr int kCMax = 4;
+// FP64-assisted butterflies for the uniform-twiddle passes (ntt_core.cuh, *_f64).  Exact and bit-identical,
+// but measured slower on B200 at 2 warps per scheduler (77.8K vs 81.4K gates/s): ptxas materialises the
+// 0x43300000 high word with a MOV / IMAD.MOV per operand.  Kept for profiling, off by default.
+#ifndef HERDB_F64_PASSES
+#define HERDB_F64_PASSES 0
+#endif
 constexpr u32 kExtStride = 1032;            // u16 words per extracted ciphertext (N + 1, padded to 16 B)
 constexpr u32 kLweMax = HERDB_N_STD128;     // largest LWE dimension supported by the smem layout
 
@@ -57,13 +64,15 @@ struct BrParams {
     u32 jobs;                    // gates_in_level * rows;  job -> gate = job / rows, row = job % rows
 };
 
+template <int C>
 struct BrSmem {
-    u32 acc[kC][2][kN];
-    u32 dig[kC][kDG2][kN];
-    u32 itw[kLaneTwWords];
-    u16 lwe[kC][kLweMax + 8];
-    u32 gate_b[kC];              // prepared b and gate code per ciphertext
-    u32 gate_code[kC];
+    u32 acc[C][2][kN];
+    u32 dig[C][kDG2][kN];
+    u32 itw[kLaneTwWords];       // inverse pass-1 lane twiddles
+    u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (re-read into registers every step)
+    u16 lwe[C][kLweMax + 8];
+    u32 gate_b[C];               // prepared b and gate code per ciphertext
+    u32 gate_code[C];
 };
 
 constexpr u32 kAccInitPos = cmulmod(kQ / 8 + 1, kNInv);             // +(Q/8+1) / N
@@ -84,8 +93,10 @@ HERDB_HD u32 operand_word(const Pool* pools, u32 pool, u32 idx, u32 flags, u32 r
 }
 
 // ------------------------------------------------------------------------------------------------
-template <class Env>
-HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 group) {
+template <int kC, class Env>
+HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32 group) {
+    constexpr u32 kThreads = 64 * kC;
+    constexpr int kChunks = 4 / kC;              // 16-byte chunks (4 evaluation points) per thread in phase B
     const u32 tid = env.tid();
     const u32 lane = tid & 31, warp = tid >> 5;
     const u32 n = P.n;
@@ -102,16 +113,19 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 gro
             if (k == n) { S.gate_b[c] = v; S.gate_code[c] = g.gate; } else S.lwe[c][k] = (u16)v;
         }
     }
-    // inverse pass-1 lane twiddles -> smem (once per group; 8 KB)
-    for (u32 w = tid; w < kLaneTwWords; w += kThreads) S.itw[w] = P.itw1[w];
-    // forward pass-2 lane twiddles -> registers (31 pairs per lane)
-    u32 ftw[62];
-#pragma unroll
-    for (int p = 0; p < 31; ++p) {
-        ftw[2 * p] = P.ftw2[((p >> 1) * 32 + lane) * 4 + (p & 1) * 2];
-        ftw[2 * p + 1] = P.ftw2[((p >> 1) * 32 + lane) * 4 + (p & 1) * 2 + 1];
-    }
+    // lane twiddles -> smem (once per group; 2 x 8 KB)
+    for (u32 w = tid; w < kLaneTwWords; w += kThreads) { S.itw[w] = P.itw1[w]; S.ftw[w] = P.ftw2[w]; }
     env.sync();
+    // forward pass-2 lane twiddles: 31 (w, w') pairs per lane, held in registers only during phase A so
+    // that phase B has the register file for its 64-bit accumulators
+    auto load_ftw = [&](u32 (&ftw)[62]) {
+#pragma unroll
+        for (int g = 0; g < 16; ++g) {
+            V4 q = *reinterpret_cast<const V4*>(&S.ftw[(g * 32 + lane) * 4]);
+            ftw[4 * g] = q.v[0]; ftw[4 * g + 1] = q.v[1];
+            if (g < 15) { ftw[4 * g + 2] = q.v[2]; ftw[4 * g + 3] = q.v[3]; }
+        }
+    };
 
     // ---- BootstrapGateCore: acc = (0, NTT(m)), m[2j] = +-(Q/8+1) depending on (b - j) in [q1, q2)
     {
@@ -132,6 +146,8 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 gro
                 const bool in = (q1 < q2) ? (temp >= q1 && temp < q2) : !(temp >= q2 && temp < q1);
                 x[k] = (coef & 1) ? 0u : (in ? kAccInitNeg : kAccInitPos);
             }
+            u32 ftw[62];
+            load_ftw(ftw);
             fwd_pass1(x);
             store_strided(S.dig[c][1], lane, x);
             env.syncwarp();
@@ -155,37 +171,62 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 gro
             store_contig(S.dig[c][j], lane, x);              // dig[c][j] doubles as transposition scratch
             env.syncwarp();
             load_strided(S.dig[c][j], lane, x);
+#if HERDB_F64_PASSES
+    #if HERDB_F64_PASSES
+        inv_pass2_f64(x);
+#else
+        inv_pass2(x);
+#endif
+#else
             inv_pass2(x);
-            int d[32];                                        // SignedDigitDecompose: centred representative
+#endif
+            // SignedDigitDecompose.  d = centred representative of the coefficient; OpenFHE peels signed
+            // 7-bit digits r_l in [-64,63] iteratively.  Equivalently d + B = sum (r_l + 64) * 128^l with
+            // B = 64*(1 + 128 + 128^2 + 128^3): the digits are the plain 7-bit fields of d + B (unique
+            // representation; |d| < Q/2 < 2^26 keeps 0 < d + B < 2^28).
+            constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
+            u32 d[32];
 #pragma unroll
             for (int k = 0; k < 32; ++k) {
                 u32 t = csub(x[k], kQ);                       // canonical [0, Q)
-                d[k] = (t < (kQ >> 1)) ? (int)t : (int)t - (int)kQ;
+                d[k] = (t < (kQ >> 1)) ? t + kB : t + (kB - kQ);
             }
             env.syncwarp();                                   // all lanes done reading the scratch
+            u32 ftw[62];
+            load_ftw(ftw);
 #pragma unroll
             for (int l = 0; l < (int)kDG; ++l) {
 #pragma unroll
-                for (int k = 0; k < 32; ++k) {
-                    int r = (int)((u32)d[k] << 25) >> 25;     // signed low 7 bits
-                    d[k] = (d[k] - r) >> 7;
-                    x[k] = (u32)(r + (int)kQ);                // r mod Q, lazily in [Q-64, Q+63]
-                }
+                for (int k = 0; k < 32; ++k) x[k] = (l == (int)kDG - 1) ? (d[k] >> (7 * l)) : ((d[k] >> (7 * l)) & 127u);
                 u32* out = S.dig[c][j + 2 * l];               // output polynomial index j + 2*l
-                fwd_pass1(x);
+#if HERDB_F64_PASSES
+                fwd_pass1_digits_f64(x);                      // raw digits r + 64; the offset is folded into stage 0
+#else
+                fwd_pass1_digits(x);
+#endif
                 store_strided(out, lane, x);
                 env.syncwarp();
                 load_contig(out, lane, x);
                 fwd_pass2(x, ftw);
-                store_contig(out, lane, x);                   // < 22Q + 2Q < 2^32, not reduced
+                store_contig(out, lane, x);                   // < 21.6Q < 2^32, not reduced
             }
         }
-        env.sync();
-        // ===== phase B: thread = evaluation points 4*tid .. 4*tid+3
+        // first key slice of phase B: issued before the barrier so that its L2 latency overlaps it
+        V4 kv_next[kChunks][2][2];
         {
-            const u32 phys = swz(4 * tid);
+            const u32* K0 = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
+#pragma unroll
+            for (int q = 0; q < kChunks; ++q)
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int jo = 0; jo < 2; ++jo) kv_next[q][s][jo] = env.ldg_v4(K0 + ((s * kDG2 + 0) * 2 + jo) * kN + 4 * q * kThreads);
+        }
+        env.sync();
+        // ===== phase B: thread = kChunks chunks of 4 evaluation points: 4*(tid + q*kThreads) ..+3
+        {
             const u32* K = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
-            u64 mac[kC][2][2][4];
+            u64 mac[kC][2][2][kChunks][4];
 #pragma unroll
             for (int c = 0; c < kC; ++c)
 #pragma unroll
@@ -193,23 +234,35 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 gro
 #pragma unroll
                     for (int jo = 0; jo < 2; ++jo)
 #pragma unroll
-                        for (int p = 0; p < 4; ++p) mac[c][s][jo][p] = 0;
+                        for (int q = 0; q < kChunks; ++q)
+#pragma unroll
+                            for (int p = 0; p < 4; ++p) mac[c][s][jo][q][p] = 0;
 #pragma unroll
             for (int r = 0; r < (int)kDG2; ++r) {
-                V4 kv[2][2];
+                V4 kv[kChunks][2][2];
 #pragma unroll
-                for (int s = 0; s < 2; ++s)
-#pragma unroll
-                    for (int jo = 0; jo < 2; ++jo) kv[s][jo] = env.ldg_v4(K + ((s * kDG2 + r) * 2 + jo) * kN);
-#pragma unroll
-                for (int c = 0; c < kC; ++c) {
-                    V4 dv = *reinterpret_cast<const V4*>(&S.dig[c][r][phys]);
+                for (int q = 0; q < kChunks; ++q)
 #pragma unroll
                     for (int s = 0; s < 2; ++s)
 #pragma unroll
-                        for (int jo = 0; jo < 2; ++jo)
+                        for (int jo = 0; jo < 2; ++jo) {
+                            kv[q][s][jo] = kv_next[q][s][jo];
+                            if (r + 1 < (int)kDG2)          // software pipeline: next digit's key words are in flight during this digit's MACs
+                                kv_next[q][s][jo] = env.ldg_v4(K + ((s * kDG2 + r + 1) * 2 + jo) * kN + 4 * q * kThreads);
+                        }
 #pragma unroll
-                            for (int p = 0; p < 4; ++p) mac[c][s][jo][p] += (u64)dv.v[p] * kv[s][jo].v[p];
+                for (int q = 0; q < kChunks; ++q) {
+                    const u32 phys = swz(4 * (tid + q * kThreads));
+#pragma unroll
+                    for (int c = 0; c < kC; ++c) {
+                        V4 dv = *reinterpret_cast<const V4*>(&S.dig[c][r][phys]);
+#pragma unroll
+                        for (int s = 0; s < 2; ++s)
+#pragma unroll
+                            for (int jo = 0; jo < 2; ++jo)
+#pragma unroll
+                                for (int p = 0; p < 4; ++p) mac[c][s][jo][q][p] += (u64)dv.v[p] * kv[q][s][jo].v[p];
+                    }
                 }
             }
 #pragma unroll
@@ -217,19 +270,24 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 gro
                 const u32 a = S.lwe[c][i];
                 const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
                 const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
-                V4 mp = env.ldg_v4(P.mono + (size_t)row_pos * kN + 4 * tid);
-                V4 mn = env.ldg_v4(P.mono + (size_t)row_neg * kN + 4 * tid);
 #pragma unroll
-                for (int jo = 0; jo < 2; ++jo) {
-                    V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys]);
+                for (int q = 0; q < kChunks; ++q) {
+                    const u32 pt = 4 * (tid + q * kThreads);
+                    const u32 phys = swz(pt);
+                    V4 mp = env.ldg_v4(P.mono + (size_t)row_pos * kN + pt);
+                    V4 mn = env.ldg_v4(P.mono + (size_t)row_neg * kN + pt);
 #pragma unroll
-                    for (int p = 0; p < 4; ++p) {
-                        u32 rp = fold62(mac[c][0][jo][p]);
-                        u32 rn = fold62(mac[c][1][jo][p]);
-                        u32 y = fold62((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
-                        av.v[p] = canon32(av.v[p] + y);
+                    for (int jo = 0; jo < 2; ++jo) {
+                        V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys]);
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) {
+                            u32 rp = fold62(mac[c][0][jo][q][p]);
+                            u32 rn = fold62(mac[c][1][jo][q][p]);
+                            u32 y = fold62((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
+                            av.v[p] = canon32(av.v[p] + y);
+                        }
+                        *reinterpret_cast<V4*>(&S.acc[c][jo][phys]) = av;
                     }
-                    *reinterpret_cast<V4*>(&S.acc[c][jo][phys]) = av;
                 }
             }
         }
@@ -246,7 +304,11 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem& S, u32 gro
         store_contig(S.dig[c][j], lane, x);
         env.syncwarp();
         load_strided(S.dig[c][j], lane, x);
+#if HERDB_F64_PASSES
+        inv_pass2_f64(x);
+#else
         inv_pass2(x);
+#endif
         if (job < P.jobs) {
             u16* ext = P.ext + (size_t)job * kExtStride;
 #pragma unroll

@@ -28,13 +28,15 @@ struct DevEnv {
     }
 };
 
-// one CTA per SM (176 KB of shared memory), persistent over groups of kC jobs
-__global__ void __launch_bounds__(kThreads, 1) blind_rotate_kernel(const __grid_constant__ BrParams P) {
+// persistent over groups of C jobs.  C = 4: one 256-thread CTA per SM (172 KB smem);
+// C = 2: two independent 128-thread CTAs per SM (88 KB each) whose phases de-synchronise.
+template <int C>
+__global__ void __launch_bounds__(64 * C, 4 / C) blind_rotate_kernel(const __grid_constant__ BrParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    BrSmem& S = *reinterpret_cast<BrSmem*>(smem_raw);
+    BrSmem<C>& S = *reinterpret_cast<BrSmem<C>*>(smem_raw);
     DevEnv env;
-    const u32 groups = (P.jobs + kC - 1) / kC;
-    for (u32 g = blockIdx.x; g < groups; g += gridDim.x) blind_rotate_group(env, P, S, g);
+    const u32 groups = (P.jobs + C - 1) / C;
+    for (u32 g = blockIdx.x; g < groups; g += gridDim.x) blind_rotate_group<C>(env, P, S, g);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -164,15 +166,27 @@ __global__ void __launch_bounds__(256) int_peak_kernel(u32* out, u32 seed, int i
 
 // ------------------------------------------------------------------------------------------------
 // launchers (plain C++ signatures so backend.cpp does not need nvcc)
-cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream) {
+template <int C>
+static cudaError_t launch_br(const BrParams& P, int sm_count, cudaStream_t stream) {
     // per device attribute; cheap enough to set on every launch (launches last milliseconds)
-    cudaError_t e = cudaFuncSetAttribute(blind_rotate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BrSmem));
+    cudaError_t e = cudaFuncSetAttribute(blind_rotate_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BrSmem<C>));
     if (e != cudaSuccess) return e;
-    const u32 groups = (P.jobs + kC - 1) / kC;
+    const u32 groups = (P.jobs + C - 1) / C;
     if (!groups) return cudaSuccess;
-    const u32 grid = groups < (u32)sm_count ? groups : (u32)sm_count;
-    blind_rotate_kernel<<<grid, kThreads, sizeof(BrSmem), stream>>>(P);
+    const u32 resident = (u32)sm_count * (4 / C);
+    const u32 grid = groups < resident ? groups : resident;
+    blind_rotate_kernel<C><<<grid, 64 * C, sizeof(BrSmem<C>), stream>>>(P);
     return cudaGetLastError();
+}
+cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream, int variant) {
+    return variant == 4 ? launch_br<4>(P, sm_count, stream) : launch_br<2>(P, sm_count, stream);
+}
+// constant-memory tables that cannot be compile-time initialised (FP64 twiddle forms); once per device
+cudaError_t upload_constants() {
+    const UniformTw64 f = make_uniform64(false), i = make_uniform64(true);
+    cudaError_t e = cudaMemcpyToSymbol(c_tw64_fwd, &f, sizeof f);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyToSymbol(c_tw64_inv, &i, sizeof i);
 }
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream) {
     if (!P.jobs) return cudaSuccess;

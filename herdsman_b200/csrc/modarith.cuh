@@ -134,3 +134,86 @@ HERDB_HD u32 modswitch_qKS_to_q(u32 v) { return ((v + 8u) >> 4) & (kLweQ - 1); }
 struct alignas(16) V4 { u32 v[4]; };
 
 }  // namespace herdb
+
+// ================================================================================================
+// FP64-assisted modular multiplication.  On B200 IMAD.HI (and IMAD.WIDE) cost two issue slots of the
+// FMA pipe, so a Shoup product (IMAD.HI, IMAD, IMAD) occupies it for 4 slots.  The quotient can be
+// computed on the otherwise idle FP64 pipe instead: for y < 2^32 held in the low word of a register
+// pair whose high word is 0x43300000, the pair read as a double is exactly 2^52 + y, and
+//     fma(2^52 + y, c, 2^52 - 2^52*c) = 2^52 + y*c   (one rounding, to an integer since ulp = 1)
+// so the low word of the result is round(y*c).  With c = round(w/Q * 2^52) / 2^52 (2^52*c is an
+// integer, hence the addend is exact) that is round(w*y/Q) up to 2^-20, and
+//     r = w*y - q*Q  (two IMADs, mod 2^32)  is the SIGNED residue of w*y with |r| <= 0.51 Q.
+// Everything stays exact: r == w*y (mod Q); only its representative differs from Shoup's.
+namespace herdb {
+
+constexpr double kTwo52 = 4503599627370496.0;
+struct F64Tw { u32 w; u32 pad; double c; double k; };       // w, c = round(w/Q*2^52)/2^52, k = 2^52 - 2^52*c
+
+inline F64Tw make_f64tw(u32 w) {
+    F64Tw t;
+    t.w = w; t.pad = 0;
+    const unsigned __int128 num = ((unsigned __int128)w << 52);
+    const u64 ci = (u64)((num + kQ / 2) / kQ);               // round(w * 2^52 / Q), < 2^52
+    t.c = (double)ci / kTwo52;                                // exact: ci < 2^53
+    t.k = kTwo52 - (double)ci;                                // exact integer
+    return t;
+}
+
+HERDB_HD double pack52(u32 lo) {                              // the double 2^52 + lo
+#if defined(__CUDA_ARCH__)
+    return __hiloint2double(0x43300000, (int)lo);
+#else
+    u64 b = 0x4330000000000000ull | lo; double d; __builtin_memcpy(&d, &b, 8); return d;
+#endif
+}
+HERDB_HD u32 lo52(double d) {
+#if defined(__CUDA_ARCH__)
+    return (u32)__double2loint(d);
+#else
+    u64 b; __builtin_memcpy(&b, &d, 8); return (u32)b;
+#endif
+}
+HERDB_HD double fma64(double a, double b, double c) {
+#if defined(__CUDA_ARCH__)
+    return __fma_rn(a, b, c);
+#else
+    return __builtin_fma(a, b, c);
+#endif
+}
+// uniform-twiddle tables in the FP64 form (index = twiddle index 1..31 as in UniformTw)
+struct UniformTw64 { F64Tw v[32]; };
+inline UniformTw64 make_uniform64(bool inverse) {
+    UniformTw64 t;
+    t.v[0] = make_f64tw(1);
+    for (u32 k = 1; k < 32; ++k) t.v[k] = make_f64tw(inverse ? ctw_inv(k) : ctw_fwd(k));
+    return t;
+}
+#if defined(__CUDACC__)
+__constant__ UniformTw64 c_tw64_fwd;        // filled by upload_constants() (kernels.cu) once per device
+__constant__ UniformTw64 c_tw64_inv;
+#endif
+inline const UniformTw64& host_tw64(bool inverse) {
+    static const UniformTw64 f = make_uniform64(false), i = make_uniform64(true);
+    return inverse ? i : f;
+}
+#if defined(__CUDA_ARCH__)
+#define HERDB_TW64F(k) c_tw64_fwd.v[k]
+#define HERDB_TW64I(k) c_tw64_inv.v[k]
+#else
+#define HERDB_TW64F(k) host_tw64(false).v[k]
+#define HERDB_TW64I(k) host_tw64(true).v[k]
+#endif
+
+// signed residue of w*y (as u32 two's complement), |r| <= 0.51 Q, any y < 2^32
+HERDB_HD u32 mul_f64(u32 w, double c, double k, u32 y) {
+    const u32 q = lo52(fma64(pack52(y), c, k));
+    return w * y - q * kQ;
+}
+// the same without the per-twiddle addend: (2^52 + y) - 2^52 is exact, then fma(y, c, 2^52)
+HERDB_HD u32 mul_f64_2op(u32 w, double c, u32 y) {
+    const u32 q = lo52(fma64(pack52(y) - kTwo52, c, kTwo52));
+    return w * y - q * kQ;
+}
+
+}  // namespace herdb

@@ -62,6 +62,67 @@ HERDB_HD void fwd_pass1(u32 (&x)[32]) {           // strided layout, stages 0..4
         }
     }
 }
+// Forward pass 1 for a signed-digit polynomial given as RAW unsigned digits u = r + 64 in [0,127]
+// (true coefficient r = u - 64, i.e. u + C with C = Q - 64 as a residue).  Stage 0 has a single
+// twiddle W1, so the offset is absorbed into its two add constants:
+//   X' = (u_x + C) + W1*(u_y + C) = u_x + W1*u_y + K1,   K1 = (C + W1*C) mod Q
+//   Y' = (u_x + C) - W1*(u_y + C) = u_x - W1*u_y + K2,   K2 = ((C - W1*C) mod Q) + 2Q
+// Outputs of stage 0 are < 3Q + 127; the remaining stages are the generic lazy ones.
+constexpr u32 kDigC = kQ - 64;
+constexpr u32 kDigCw = cmulmod(ctw_fwd(1), kDigC);
+constexpr u32 kDigK1 = (kDigC + kDigCw) % kQ;
+constexpr u32 kDigK2 = (kDigC + kQ - kDigCw) % kQ + kQ2;
+HERDB_HD void fwd_pass1_digits(u32 (&x)[32]) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[k + 16]);
+        u32 u = x[k];
+        x[k] = u + v + kDigK1;
+        x[k + 16] = u - v + kDigK2;
+    }
+#pragma unroll
+    for (int s = 1; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+            u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[k + h]);
+            u32 u = x[k];
+            x[k] = u + v;
+            x[k + h] = u - v + kQ2;
+        }
+    }
+}
+// The same pass with the quotient of every product taken on the FP64 pipe (modarith.cuh, mul_f64):
+// each product is the signed residue r, |r| <= 0.51 Q, so a stage moves a value by at most 0.51 Q in
+// either direction.  Stage 0 adds 8Q on top of the digit offset: outputs of stage 0 lie in
+// [7.49Q, 9.51Q + 127], outputs of the pass in [5.4Q, 11.6Q]; the five lazy Shoup stages of pass 2
+// then end below 21.6Q < 2^32, and 8 * 21.6Q * Q < 2^62 keeps the 64-bit MAC exact.
+constexpr u32 kDigK1f = (kDigC + kDigCw) % kQ + 8 * kQ;
+constexpr u32 kDigK2f = (kDigC + kQ - kDigCw) % kQ + 8 * kQ;
+HERDB_HD void fwd_pass1_digits_f64(u32 (&x)[32]) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        u32 r = mul_f64(HERDB_TW64F(1).w, HERDB_TW64F(1).c, HERDB_TW64F(1).k, x[k + 16]);
+        u32 u = x[k];
+        x[k] = u + r + kDigK1f;
+        x[k + 16] = u - r + kDigK2f;
+    }
+#pragma unroll
+    for (int s = 1; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+            u32 r = mul_f64(HERDB_TW64F(idx).w, HERDB_TW64F(idx).c, HERDB_TW64F(idx).k, x[k + h]);
+            u32 u = x[k];
+            x[k] = u + r;
+            x[k + h] = u - r;
+        }
+    }
+}
 HERDB_HD void fwd_pass2(u32 (&x)[32], const u32 (&tw)[62]) {   // contiguous layout, stages 5..9
     int off = 0;
 #pragma unroll
@@ -107,6 +168,22 @@ HERDB_HD void inv_pass2(u32 (&x)[32]) {           // strided layout, strides 32.
             u32 u = x[k], v = x[k + h];
             x[k] = csub(u + v, kQ2);
             x[k + h] = mul_shoup_lazy(HERDB_TWI(idx, 0), HERDB_TWI(idx, 1), u - v + kQ2);
+        }
+    }
+}
+
+// FP64-quotient form of the same pass: the product r is a signed residue, |r| <= 0.51 Q, and r + Q keeps
+// the [0, 2Q) invariant (the +Q rides on the first IMAD's addend)
+HERDB_HD void inv_pass2_f64(u32 (&x)[32]) {
+#pragma unroll
+    for (int h = 1; h <= 16; h <<= 1) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = 16 / h + k / (2 * h);
+            u32 u = x[k], v = x[k + h];
+            x[k] = csub(u + v, kQ2);
+            x[k + h] = mul_f64(HERDB_TW64I(idx).w, HERDB_TW64I(idx).c, HERDB_TW64I(idx).k, u - v + kQ2) + kQ;
         }
     }
 }

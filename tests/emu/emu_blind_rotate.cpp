@@ -21,16 +21,18 @@ struct HostEnv {
     V4 ldg_v4(const u32* p) const { return *reinterpret_cast<const V4*>(p); }
 };
 
-struct ThreadArg { HostEnv env; const BrParams* P; BrSmem* S; u32 groups; };
+template <int C> struct ThreadArg { HostEnv env; const BrParams* P; BrSmem<C>* S; u32 groups; };
 
-static void* thread_main(void* a) {
-    ThreadArg* t = (ThreadArg*)a;
-    for (u32 g = 0; g < t->groups; ++g) blind_rotate_group(t->env, *t->P, *t->S, g);
+template <int C> static void* thread_main(void* a) {
+    ThreadArg<C>* t = (ThreadArg<C>*)a;
+    for (u32 g = 0; g < t->groups; ++g) blind_rotate_group<C>(t->env, *t->P, *t->S, g);
     return nullptr;
 }
 
-extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
-                                u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
+template <int C>
+static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
+                   u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
+    constexpr int kC = C; constexpr int kThreads = 64 * C;
     const herdb_key_header* h = (const herdb_key_header*)blob;
     if (len < sizeof *h || h->magic != HERDB_KEY_MAGIC) return -1;
     const u32 n = h->n;
@@ -52,20 +54,31 @@ extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u1
     P.pools[1] = Pool{const_cast<u16*>(ct_b), 1, 0};
     std::vector<u16> ext((size_t)batch * kExtStride);
     P.ext = ext.data(); P.trace = trace_out; P.n = n; P.steps = steps; P.rows = batch; P.jobs = batch;
-    BrSmem* S = new BrSmem;
-    pthread_barrier_t cta, warps[8];
+    BrSmem<C>* S = new BrSmem<C>;
+    pthread_barrier_t cta, warps[2 * C];
     pthread_barrier_init(&cta, nullptr, kThreads);
     for (auto& w : warps) pthread_barrier_init(&w, nullptr, 32);
-    std::vector<ThreadArg> args(kThreads);
+    std::vector<ThreadArg<C>> args(kThreads);
     std::vector<pthread_t> th(kThreads);
     u32 groups = (batch + kC - 1) / kC;
     pthread_attr_t attr; pthread_attr_init(&attr); pthread_attr_setstacksize(&attr, 1 << 20);
     for (u32 t = 0; t < (u32)kThreads; ++t) {
-        args[t] = ThreadArg{HostEnv{t, &cta, warps}, &P, S, groups};
-        pthread_create(&th[t], &attr, thread_main, &args[t]);
+        args[t] = ThreadArg<C>{HostEnv{t, &cta, warps}, &P, S, groups};
+        pthread_create(&th[t], &attr, thread_main<C>, &args[t]);
     }
     for (auto& t : th) pthread_join(t, nullptr);
     for (u32 b = 0; b < batch; ++b) memcpy(ext_out + (size_t)b * (kN + 1), &ext[(size_t)b * kExtStride], (kN + 1) * 2);
     delete S;
     return 0;
+}
+
+// variant = ciphertexts per CTA (2 or 4), as HERDB_BR_VARIANT selects in the product
+extern "C" int emu_blind_rotate_v(int variant, const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
+                                  u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
+    return variant == 4 ? emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out)
+                        : emu_run<2>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
+}
+extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
+                                u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
+    return emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
 }
