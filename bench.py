@@ -42,6 +42,26 @@ KS_BYTES_PER_GATE = 1024 * 2 * (N_LWE + 1) * 2
 CT_BYTES = (N_LWE + 1) * 2
 
 
+_JSON_FD = None
+
+
+def guard_stdout():
+    """Libraries (NCCL's version banner, torchrun warnings) write to fd 1; the driver wants ONE JSON line there.
+    Everything written to stdout from here on goes to stderr, the JSON line goes to the original fd."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def clocks_sampler(stop, out, gpu_index):
     q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
@@ -99,7 +119,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": v, "unit": "gates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -186,6 +206,9 @@ def run_ours(args, rank, world, local_rank):
     ok_e2e = np.array_equal(api.client_decrypt_bits(N_LWE, sk, h_out.numpy()), 1 - (bits_a & bits_b))
     if not (ok_dev and ok_e2e):
         raise SystemExit("bench: decrypted outputs do not match NAND of the inputs")
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
 
@@ -227,7 +250,7 @@ def run_ours(args, rank, world, local_rank):
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(be, sk, args)
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def cpu_baseline(be, sk, args):
@@ -264,6 +287,7 @@ def main():
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    guard_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:

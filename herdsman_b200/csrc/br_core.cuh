@@ -28,12 +28,6 @@ namespace herdb {
 // ciphertexts per CTA is a template parameter C (2 or 4); a CTA has 64*C threads = 2*C warps, one
 // warp per (ciphertext, component) polynomial in phase A, 16/C evaluation points per thread in phase B
 constexpr int kCMax = 4;
-// FP64-assisted butterflies for the uniform-twiddle passes (ntt_core.cuh, *_f64).  Exact and bit-identical,
-// but measured slower on B200 at 2 warps per scheduler (77.8K vs 81.4K gates/s): ptxas materialises the
-// 0x43300000 high word with a MOV / IMAD.MOV per operand.  Kept for profiling, off by default.
-#ifndef HERDB_F64_PASSES
-#define HERDB_F64_PASSES 0
-#endif
 constexpr u32 kExtStride = 1032;            // u16 words per extracted ciphertext (N + 1, padded to 16 B)
 constexpr u32 kLweMax = HERDB_N_STD128;     // largest LWE dimension supported by the smem layout
 
@@ -69,7 +63,7 @@ struct BrSmem {
     u32 acc[C][2][kN];
     u32 dig[C][kDG2][kN];
     u32 itw[kLaneTwWords];       // inverse pass-1 lane twiddles
-    u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (re-read into registers every step)
+    u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (streamed by fwd_pass2_stream)
     u16 lwe[C][kLweMax + 8];
     u32 gate_b[C];               // prepared b and gate code per ciphertext
     u32 gate_code[C];
@@ -116,17 +110,6 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
     // lane twiddles -> smem (once per group; 2 x 8 KB)
     for (u32 w = tid; w < kLaneTwWords; w += kThreads) { S.itw[w] = P.itw1[w]; S.ftw[w] = P.ftw2[w]; }
     env.sync();
-    // forward pass-2 lane twiddles: 31 (w, w') pairs per lane, held in registers only during phase A so
-    // that phase B has the register file for its 64-bit accumulators
-    auto load_ftw = [&](u32 (&ftw)[62]) {
-#pragma unroll
-        for (int g = 0; g < 16; ++g) {
-            V4 q = *reinterpret_cast<const V4*>(&S.ftw[(g * 32 + lane) * 4]);
-            ftw[4 * g] = q.v[0]; ftw[4 * g + 1] = q.v[1];
-            if (g < 15) { ftw[4 * g + 2] = q.v[2]; ftw[4 * g + 3] = q.v[3]; }
-        }
-    };
-
     // ---- BootstrapGateCore: acc = (0, NTT(m)), m[2j] = +-(Q/8+1) depending on (b - j) in [q1, q2)
     {
         const int c = warp >> 1, j = warp & 1;
@@ -146,13 +129,11 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 const bool in = (q1 < q2) ? (temp >= q1 && temp < q2) : !(temp >= q2 && temp < q1);
                 x[k] = (coef & 1) ? 0u : (in ? kAccInitNeg : kAccInitPos);
             }
-            u32 ftw[62];
-            load_ftw(ftw);
             fwd_pass1(x);
             store_strided(S.dig[c][1], lane, x);
             env.syncwarp();
             load_contig(S.dig[c][1], lane, x);
-            fwd_pass2(x, ftw);
+            fwd_pass2_stream(x, S.ftw, lane);
 #pragma unroll
             for (int k = 0; k < 32; ++k) x[k] = canon32(x[k]);
             store_contig(S.acc[c][1], lane, x);
@@ -171,15 +152,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             store_contig(S.dig[c][j], lane, x);              // dig[c][j] doubles as transposition scratch
             env.syncwarp();
             load_strided(S.dig[c][j], lane, x);
-#if HERDB_F64_PASSES
-    #if HERDB_F64_PASSES
-        inv_pass2_f64(x);
-#else
-        inv_pass2(x);
-#endif
-#else
             inv_pass2(x);
-#endif
             // SignedDigitDecompose.  d = centred representative of the coefficient; OpenFHE peels signed
             // 7-bit digits r_l in [-64,63] iteratively.  Equivalently d + B = sum (r_l + 64) * 128^l with
             // B = 64*(1 + 128 + 128^2 + 128^3): the digits are the plain 7-bit fields of d + B (unique
@@ -192,23 +165,17 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 d[k] = (t < (kQ >> 1)) ? t + kB : t + (kB - kQ);
             }
             env.syncwarp();                                   // all lanes done reading the scratch
-            u32 ftw[62];
-            load_ftw(ftw);
 #pragma unroll
             for (int l = 0; l < (int)kDG; ++l) {
 #pragma unroll
                 for (int k = 0; k < 32; ++k) x[k] = (l == (int)kDG - 1) ? (d[k] >> (7 * l)) : ((d[k] >> (7 * l)) & 127u);
                 u32* out = S.dig[c][j + 2 * l];               // output polynomial index j + 2*l
-#if HERDB_F64_PASSES
-                fwd_pass1_digits_f64(x);                      // raw digits r + 64; the offset is folded into stage 0
-#else
-                fwd_pass1_digits(x);
-#endif
+                fwd_pass1_digits(x);                          // raw digits r + 64; the offset is folded into stage 0
                 store_strided(out, lane, x);
                 env.syncwarp();
                 load_contig(out, lane, x);
-                fwd_pass2(x, ftw);
-                store_contig(out, lane, x);                   // < 21.6Q < 2^32, not reduced
+                fwd_pass2_stream(x, S.ftw, lane);            // lane twiddles streamed from smem: measured faster than
+                store_contig(out, lane, x);                   // holding 62 twiddle registers; < 22Q < 2^32, not reduced
             }
         }
         // first key slice of phase B: issued before the barrier so that its L2 latency overlaps it
@@ -304,11 +271,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
         store_contig(S.dig[c][j], lane, x);
         env.syncwarp();
         load_strided(S.dig[c][j], lane, x);
-#if HERDB_F64_PASSES
-        inv_pass2_f64(x);
-#else
         inv_pass2(x);
-#endif
         if (job < P.jobs) {
             u16* ext = P.ext + (size_t)job * kExtStride;
 #pragma unroll

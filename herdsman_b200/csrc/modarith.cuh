@@ -217,3 +217,45 @@ HERDB_HD u32 mul_f64_2op(u32 w, double c, u32 y) {
 }
 
 }  // namespace herdb
+
+// ================================================================================================
+// FP64 quotient, modulus-2Q form (the one the blind-rotation kernel uses).  With c = ci / 2^52,
+// ci = round(w * 2^52 / 2Q) < 2^51, and Y = 2^52 + y (y < 2^32 in the low word of a register pair
+// whose high word is 0x43300000):
+//     fma(Y, c, 2^52) = 2^52 + ci + round(y*c)          (one rounding, ulp = 1, sum < 2^53)
+// so its low word is  low = lo32(ci) + q  (mod 2^32),  q = round(y*w/2Q) +- 2^-21, and
+//     r0 = w*y - low*2Q   (two IMADs, mod 2^32),   r0 + E == w*y - q*2Q,   E = lo32(ci)*2Q mod 2^32
+// is the SIGNED residue of w*y modulo 2Q (hence modulo Q), |r0 + E| <= Q + 128.  The addend of the
+// DFMA is the same for every twiddle, E rides on the butterfly's adds (a constant-bank operand for
+// lane-uniform twiddles).  Exactness never depends on the rounding; only the range bound does.
+namespace herdb {
+constexpr u32 kF64Slack = 128;                                // |r| <= Q + kF64Slack
+struct F64U { u32 w, E, nE, pad; double c; };                 // nE = -E mod 2^32
+inline F64U make_f64u(u32 w) {
+    F64U t;
+    const unsigned __int128 num = ((unsigned __int128)w << 52);
+    const u64 ci = (u64)((num + kQ) / (2ull * kQ));           // round(w * 2^52 / 2Q)
+    t.w = w; t.c = (double)ci / kTwo52;                       // exact (ci < 2^53)
+    t.E = (u32)ci * kQ2; t.nE = 0u - t.E; t.pad = 0;
+    return t;
+}
+HERDB_HD double with_lo(double d, u32 lo) {                   // replace the low word of a register pair
+#if defined(__CUDA_ARCH__)
+    return __hiloint2double(__double2hiint(d), (int)lo);
+#else
+    u64 b; __builtin_memcpy(&b, &d, 8); b = (b & 0xFFFFFFFF00000000ull) | lo; __builtin_memcpy(&d, &b, 8); return d;
+#endif
+}
+HERDB_HD double mk_double(u32 hi, u32 lo) {
+#if defined(__CUDA_ARCH__)
+    return __hiloint2double((int)hi, (int)lo);
+#else
+    u64 b = ((u64)hi << 32) | lo; double d; __builtin_memcpy(&d, &b, 8); return d;
+#endif
+}
+// r0 of the text: y in the low word of pair yd
+HERDB_HD u32 mul_q2(u32 w, double c, double yd) {
+    const u32 low = lo52(fma64(yd, c, kTwo52));
+    return w * lo52(yd) - low * kQ2;
+}
+}  // namespace herdb
