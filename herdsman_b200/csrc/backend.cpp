@@ -75,7 +75,7 @@ int run_level(herdb_ctx* ctx, Device& d, const DeviceKey& key, const GateDesc* d
     for (int i = 0; i < 4; ++i) bp.pools[i] = pools[i];
     bp.ext = d.ext; bp.trace = d_trace; bp.n = key.n; bp.steps = std::min(steps, key.n); bp.rows = rows; bp.jobs = jobs;
     int rc = timed_begin(ctx, d, 0); if (rc) return rc;
-    CU(launch_blind_rotate(bp, d.sm_count, d.stream, ctx->br_variant));
+    CU(launch_blind_rotate(bp, d.sm_count, d.stream));
     rc = timed_end(ctx, d); if (rc) return rc;
     KsParams kp{};
     kp.ksk = key.ksk; kp.ext = d.ext; kp.gates = d_gates;
@@ -205,8 +205,6 @@ extern "C" int herdb_create(herdb_ctx** out, const int* device_ids, int n_device
     ctx->key_dir = key_dir ? key_dir : "";
     const char* mb = getenv("HERDB_MEM_BUDGET_MB");
     ctx->mem_budget = (size_t)(mb ? atoll(mb) : 16384) << 20;
-    const char* var = getenv("HERDB_BR_VARIANT");            // ciphertexts per CTA: 4 (default) or 2
-    ctx->br_variant = (var && atoi(var) == 2) ? 2 : 4;
     std::vector<int> ids;
     if (device_ids && n_devices > 0) ids.assign(device_ids, device_ids + n_devices); else ids.push_back(0);
     std::vector<u32> mono, ftw2(kLaneTwWords), itw1(kLaneTwWords);

@@ -62,7 +62,6 @@ struct herdb_ctx {
     std::string storage_dir, key_dir;
     mutable std::mutex err_mu;
     std::string last_error;
-    int br_variant = 4;          // ciphertexts per blind-rotation CTA (HERDB_BR_VARIANT)
     size_t mem_budget = 0;       // bytes of scratch per device for slots + ext
     // task queue (herdb_map_async)
     std::mutex q_mu;

@@ -64,6 +64,7 @@ struct BrSmem {
     u32 dig[C][kDG2][kN];
     u32 itw[kLaneTwWords];       // inverse pass-1 lane twiddles
     u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (streamed by fwd_pass2_stream)
+    u32 kst[2][4][kN];           // bootstrapping-key staging ring (cp.async): two digits x (sign, column) x 1024 points
     u16 lwe[C][kLweMax + 8];
     u32 gate_b[C];               // prepared b and gate code per ciphertext
     u32 gate_code[C];
@@ -90,7 +91,7 @@ HERDB_HD u32 operand_word(const Pool* pools, u32 pool, u32 idx, u32 flags, u32 r
 template <int kC, class Env>
 HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32 group) {
     constexpr u32 kThreads = 64 * kC;
-    constexpr int kChunks = 4 / kC;              // 16-byte chunks (4 evaluation points) per thread in phase B
+    static_assert(kC == 4, "the key staging scheme recycles four digit slots for the four (sign, column) pieces");
     const u32 tid = env.tid();
     const u32 lane = tid & 31, warp = tid >> 5;
     const u32 n = P.n;
@@ -143,6 +144,20 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 
     // ---- EvalAcc: n CMUX steps (AddToAccCGGI)
     for (u32 i = 0; i < P.steps; ++i) {
+        // Key slice of this step, staged by cp.async.  A thread copies exactly the 16-byte pieces it will
+        // consume (4 (sign, column) pieces per digit), so completion needs cp.async.wait_group only, no
+        // barrier.  Digits 0 and 1 go to the staging ring now and land during phase A; later digits are
+        // issued inside phase B into the ring and into the digit slots this thread has already consumed.
+        const u32* K = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
+        const u32 phys_b = swz(4 * tid);
+        auto stage_key = [&](int r, u32* dst0, u32 dst_stride) {      // piece (s, jo) of digit r -> dst0 + (2*s + jo)*dst_stride
+#pragma unroll
+            for (int s = 0; s < 2; ++s)
+#pragma unroll
+                for (int jo = 0; jo < 2; ++jo) env.cp16(dst0 + (2 * s + jo) * dst_stride, K + ((s * kDG2 + r) * 2 + jo) * kN);
+        };
+        stage_key(0, &S.kst[0][0][phys_b], kN); env.cp_commit();
+        stage_key(1, &S.kst[1][0][phys_b], kN); env.cp_commit();
         // ===== phase A: warp = (ciphertext c, component j)
         {
             const int c = warp >> 1, j = warp & 1;
@@ -178,22 +193,10 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 store_contig(out, lane, x);                   // holding 62 twiddle registers; < 22Q < 2^32, not reduced
             }
         }
-        // first key slice of phase B: issued before the barrier so that its L2 latency overlaps it
-        V4 kv_next[kChunks][2][2];
-        {
-            const u32* K0 = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
-#pragma unroll
-            for (int q = 0; q < kChunks; ++q)
-#pragma unroll
-                for (int s = 0; s < 2; ++s)
-#pragma unroll
-                    for (int jo = 0; jo < 2; ++jo) kv_next[q][s][jo] = env.ldg_v4(K0 + ((s * kDG2 + 0) * 2 + jo) * kN + 4 * q * kThreads);
-        }
         env.sync();
         // ===== phase B: thread = kChunks chunks of 4 evaluation points: 4*(tid + q*kThreads) ..+3
         {
-            const u32* K = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
-            u64 mac[kC][2][2][kChunks][4];
+            u64 mac[kC][2][2][4];
 #pragma unroll
             for (int c = 0; c < kC; ++c)
 #pragma unroll
@@ -201,35 +204,40 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 #pragma unroll
                     for (int jo = 0; jo < 2; ++jo)
 #pragma unroll
-                        for (int q = 0; q < kChunks; ++q)
-#pragma unroll
-                            for (int p = 0; p < 4; ++p) mac[c][s][jo][q][p] = 0;
+                        for (int p = 0; p < 4; ++p) mac[c][s][jo][p] = 0;
+            // where digit r's key pieces live: r = 0,2,6 ring 0; r = 1,4 ring 1; r = 3,5,7 the consumed digit slots 0,1,2
 #pragma unroll
             for (int r = 0; r < (int)kDG2; ++r) {
-                V4 kv[kChunks][2][2];
+                if (r == 0 || r == 1 || r == 2 || r == 4) env.cp_wait1();      // groups: {0} {1} | {2,3} | {4,5} | {6,7}
+                if (r == 6) env.cp_wait0();
+                const u32* kbase = (r == 0 || r == 2 || r == 6) ? &S.kst[0][0][phys_b]
+                                 : (r == 1 || r == 4)           ? &S.kst[1][0][phys_b]
+                                                                : &S.dig[0][(r - 3) / 2][phys_b];
+                const u32 kstride = (r == 3 || r == 5 || r == 7) ? (u32)(kDG2 * kN) : kN;
+                V4 kv[2][2];
 #pragma unroll
-                for (int q = 0; q < kChunks; ++q)
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int jo = 0; jo < 2; ++jo) kv[s][jo] = *reinterpret_cast<const V4*>(kbase + (2 * s + jo) * kstride);
+                u32 dep = 0;
+#pragma unroll
+                for (int c = 0; c < kC; ++c) {
+                    V4 dv = *reinterpret_cast<const V4*>(&S.dig[c][r][phys_b]);
+                    dep |= dv.v[0];
 #pragma unroll
                     for (int s = 0; s < 2; ++s)
 #pragma unroll
-                        for (int jo = 0; jo < 2; ++jo) {
-                            kv[q][s][jo] = kv_next[q][s][jo];
-                            if (r + 1 < (int)kDG2)          // software pipeline: next digit's key words are in flight during this digit's MACs
-                                kv_next[q][s][jo] = env.ldg_v4(K + ((s * kDG2 + r + 1) * 2 + jo) * kN + 4 * q * kThreads);
-                        }
+                        for (int jo = 0; jo < 2; ++jo)
 #pragma unroll
-                for (int q = 0; q < kChunks; ++q) {
-                    const u32 phys = swz(4 * (tid + q * kThreads));
-#pragma unroll
-                    for (int c = 0; c < kC; ++c) {
-                        V4 dv = *reinterpret_cast<const V4*>(&S.dig[c][r][phys]);
-#pragma unroll
-                        for (int s = 0; s < 2; ++s)
-#pragma unroll
-                            for (int jo = 0; jo < 2; ++jo)
-#pragma unroll
-                                for (int p = 0; p < 4; ++p) mac[c][s][jo][q][p] += (u64)dv.v[p] * kv[q][s][jo].v[p];
-                    }
+                            for (int p = 0; p < 4; ++p) mac[c][s][jo][p] += (u64)dv.v[p] * kv[s][jo].v[p];
+                }
+                // digit r is consumed: its slots (and the ring stage it came from) take the next pieces.  The
+                // asm operands make the copies wait for this iteration's shared-memory reads (dep, kv).
+                if (r <= 2) {
+                    env.cp_fence(dep ^ kv[1][1].v[0]);
+                    stage_key(2 * r + 2, &S.kst[r & 1][0][phys_b], kN);
+                    stage_key(2 * r + 3, &S.dig[0][r][phys_b], kDG2 * kN);
+                    env.cp_commit();
                 }
             }
 #pragma unroll
@@ -237,24 +245,19 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 const u32 a = S.lwe[c][i];
                 const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
                 const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
+                V4 mp = env.ldg_v4(P.mono + (size_t)row_pos * kN + 4 * tid);
+                V4 mn = env.ldg_v4(P.mono + (size_t)row_neg * kN + 4 * tid);
 #pragma unroll
-                for (int q = 0; q < kChunks; ++q) {
-                    const u32 pt = 4 * (tid + q * kThreads);
-                    const u32 phys = swz(pt);
-                    V4 mp = env.ldg_v4(P.mono + (size_t)row_pos * kN + pt);
-                    V4 mn = env.ldg_v4(P.mono + (size_t)row_neg * kN + pt);
+                for (int jo = 0; jo < 2; ++jo) {
+                    V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys_b]);
 #pragma unroll
-                    for (int jo = 0; jo < 2; ++jo) {
-                        V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys]);
-#pragma unroll
-                        for (int p = 0; p < 4; ++p) {
-                            u32 rp = fold62(mac[c][0][jo][q][p]);
-                            u32 rn = fold62(mac[c][1][jo][q][p]);
-                            u32 y = fold62((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
-                            av.v[p] = canon32(av.v[p] + y);
-                        }
-                        *reinterpret_cast<V4*>(&S.acc[c][jo][phys]) = av;
+                    for (int p = 0; p < 4; ++p) {
+                        u32 rp = fold62(mac[c][0][jo][p]);
+                        u32 rn = fold62(mac[c][1][jo][p]);
+                        u32 y = fold62((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
+                        av.v[p] = canon32(av.v[p] + y);
                     }
+                    *reinterpret_cast<V4*>(&S.acc[c][jo][phys_b]) = av;
                 }
             }
         }

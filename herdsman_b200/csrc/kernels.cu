@@ -26,12 +26,20 @@ struct DevEnv {
         V4 r; r.v[0] = q.x; r.v[1] = q.y; r.v[2] = q.z; r.v[3] = q.w;
         return r;
     }
+    // 16-byte asynchronous global -> shared copy (LDGSTS, L2 only), grouped by commit / wait_group
+    __device__ __forceinline__ void cp16(u32* smem_dst, const u32* gsrc) const {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((u32)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+    }
+    __device__ __forceinline__ void cp_commit() const { asm volatile("cp.async.commit_group;" ::: "memory"); }
+    __device__ __forceinline__ void cp_wait1() const { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+    __device__ __forceinline__ void cp_wait0() const { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+    // orders the copies that follow after the shared-memory reads whose results feed `dep`
+    __device__ __forceinline__ void cp_fence(u32 dep) const { asm volatile("" ::"r"(dep) : "memory"); }
 };
 
-// persistent over groups of C jobs.  C = 4: one 256-thread CTA per SM (172 KB smem);
-// C = 2: two independent 128-thread CTAs per SM (88 KB each) whose phases de-synchronise.
+// persistent over groups of C = 4 jobs: one 256-thread CTA per SM (212 KB of shared memory)
 template <int C>
-__global__ void __launch_bounds__(64 * C, 4 / C) blind_rotate_kernel(const __grid_constant__ BrParams P) {
+__global__ void __launch_bounds__(64 * C, 1) blind_rotate_kernel(const __grid_constant__ BrParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BrSmem<C>& S = *reinterpret_cast<BrSmem<C>*>(smem_raw);
     DevEnv env;
@@ -173,13 +181,13 @@ static cudaError_t launch_br(const BrParams& P, int sm_count, cudaStream_t strea
     if (e != cudaSuccess) return e;
     const u32 groups = (P.jobs + C - 1) / C;
     if (!groups) return cudaSuccess;
-    const u32 resident = (u32)sm_count * (4 / C);
+    const u32 resident = (u32)sm_count;
     const u32 grid = groups < resident ? groups : resident;
     blind_rotate_kernel<C><<<grid, 64 * C, sizeof(BrSmem<C>), stream>>>(P);
     return cudaGetLastError();
 }
-cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream, int variant) {
-    return variant == 4 ? launch_br<4>(P, sm_count, stream) : launch_br<2>(P, sm_count, stream);
+cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream) {
+    return launch_br<4>(P, sm_count, stream);
 }
 // constant-memory tables that cannot be compile-time initialised (FP64 twiddle forms); once per device
 cudaError_t upload_constants() {

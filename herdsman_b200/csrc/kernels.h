@@ -21,8 +21,7 @@ struct GatherParams {
     u32 n, rows, out_bits;
 };
 
-// variant = ciphertexts per CTA (2 or 4)
-cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream, int variant);
+cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream);
 cudaError_t upload_constants();      // call once per device before the first launch
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream);
 cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream);

@@ -19,6 +19,25 @@ struct HostEnv {
     void sync() { pthread_barrier_wait(cta); }
     void syncwarp() { pthread_barrier_wait(&warps[tid_ >> 5]); }
     V4 ldg_v4(const u32* p) const { return *reinterpret_cast<const V4*>(p); }
+    // cp.async model that exposes both hazards: the destination is poisoned when the copy is issued (a
+    // late reader of the old contents sees garbage) and filled only when a wait_group covers its group
+    // (an early reader of the new contents sees garbage too)
+    struct Pending { u32* dst; const u32* src; u32 group; };
+    std::vector<Pending> pend;
+    u32 committed = 0;
+    void cp16(u32* dst, const u32* src) { for (int k = 0; k < 4; ++k) dst[k] = 0xDEADBEEFu; pend.push_back({dst, src, committed}); }
+    void cp_commit() { ++committed; }
+    void complete(u32 keep) {
+        size_t w = 0;
+        for (size_t k = 0; k < pend.size(); ++k) {
+            if (pend[k].group + keep < committed) memcpy(pend[k].dst, pend[k].src, 16);
+            else pend[w++] = pend[k];
+        }
+        pend.resize(w);
+    }
+    void cp_wait1() { complete(1); }
+    void cp_wait0() { complete(0); }
+    void cp_fence(u32) {}
 };
 
 template <int C> struct ThreadArg { HostEnv env; const BrParams* P; BrSmem<C>* S; u32 groups; };
@@ -72,12 +91,6 @@ static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, cons
     return 0;
 }
 
-// variant = ciphertexts per CTA (2 or 4), as HERDB_BR_VARIANT selects in the product
-extern "C" int emu_blind_rotate_v(int variant, const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
-                                  u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
-    return variant == 4 ? emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out)
-                        : emu_run<2>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
-}
 extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
                                 u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
     return emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);

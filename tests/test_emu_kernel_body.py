@@ -18,30 +18,29 @@ EMU_DIR = os.path.join(os.path.dirname(__file__), "emu")
 def emu():
     subprocess.run(["make", "-C", EMU_DIR], check=True, capture_output=True)
     L = C.CDLL(os.path.join(EMU_DIR, "libemu.so"))
-    L.emu_blind_rotate_v.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+    L.emu_blind_rotate.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
     return L
 
 
-def _run(emu, blob, gate, ca, cb, steps, variant=2):
+def _run(emu, blob, gate, ca, cb, steps):
     B = ca.shape[0]
     ext = np.zeros((B, 1025), np.uint16); trace = np.zeros((B, 2, 1024), np.uint32)
-    rc = emu.emu_blind_rotate_v(variant, blob.ctypes.data, blob.size, po.GATE[gate], ca.ctypes.data, cb.ctypes.data, B, steps,
+    rc = emu.emu_blind_rotate(blob.ctypes.data, blob.size, po.GATE[gate], ca.ctypes.data, cb.ctypes.data, B, steps,
                               ext.ctypes.data, trace.ctypes.data)
     assert rc == 0
     return ext, trace
 
 
-@pytest.mark.parametrize("variant", [2, 4])
 @pytest.mark.parametrize("gate,steps", [("NAND", 0), ("NAND", 1), ("NAND", 2), ("NAND", 32), ("AND", 32), ("OR", 32),
                                         ("NOR", 32), ("XOR_FAST", 32), ("XNOR_FAST", 5)])
-def test_emulated_kernel_body_matches_oracle(emu, test_key, gate, steps, variant):
+def test_emulated_kernel_body_matches_oracle(emu, test_key, gate, steps):
     n, sk, blob = test_key["n"], test_key["sk"], test_key["blob"]
     o = po.Oracle(blob)
     rng = np.random.default_rng(5)
     B = 6                                              # two groups of 4, the second one ragged
     a = rng.integers(0, 2, B).astype(np.uint8); b = rng.integers(0, 2, B).astype(np.uint8)
     ca = po.encrypt_bits(n, sk, a, first=0); cb = po.encrypt_bits(n, sk, b, first=100)
-    ext, trace = _run(emu, blob, gate, ca, cb, steps, variant)
+    ext, trace = _run(emu, blob, gate, ca, cb, steps)
     for i in range(B):
         assert np.array_equal(o.blind_rotate_trace(gate, ca[i], cb[i], steps).reshape(2, 1024), trace[i]), (gate, steps, i)
         if steps == n:
