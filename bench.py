@@ -151,7 +151,9 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.empty_cache()
 
     # ---- synthetic encrypted inputs (per rank), pinned on the host and resident in HBM
-    B = args.batch
+    # whole waves of the persistent kernel: one CTA per SM, 4 ciphertexts per CTA
+    wave = 4 * torch.cuda.get_device_properties(dev).multi_processor_count
+    B = args.batch if args.batch else -(-32768 // wave) * wave
     w = N_LWE + 1
     rng = np.random.default_rng(100 + rank)
     bits_a = rng.integers(0, 2, B).astype(np.uint8); bits_b = rng.integers(0, 2, B).astype(np.uint8)
@@ -280,7 +282,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=32768, help="gates per step per GPU")
+    ap.add_argument("--batch", type=int, default=0, help="gates per step per GPU (default: 32768 rounded up to whole waves of 4 x SM count)")
     ap.add_argument("--ref-gates", type=int, default=0, help="reference arm: gates per step (default 2 x cores)")
     ap.add_argument("--cpu-gates-per-core", type=int, default=48)
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -233,6 +233,8 @@ class Backend:
     def eval_circuit_rows(self, session, circuit: Circuit, rows_in, out=None):
         n = self.key_lwe_n(session)
         n_rows = rows_in.shape[0]
+        if isinstance(rows_in, np.ndarray):
+            rows_in = np.ascontiguousarray(rows_in)      # column slices of a wider frame are views
         if out is None:
             out = np.empty((n_rows, circuit.out_bits, n + 1), np.uint16)
         cc = circuit.to_c()

@@ -219,7 +219,6 @@ extern "C" int herdb_create(herdb_ctx** out, const int* device_ids, int n_device
         if (cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(HERDB_ERR_CUDA);
         if (cudaMalloc((void**)&d->mono, mono.size() * 4) != cudaSuccess || cudaMalloc((void**)&d->ftw2, kLaneTwWords * 4) != cudaSuccess ||
             cudaMalloc((void**)&d->itw1, kLaneTwWords * 4) != cudaSuccess) return fail(HERDB_ERR_NOMEM);
-        if (upload_constants() != cudaSuccess) return fail(HERDB_ERR_CUDA);
         cudaMemcpy(d->mono, mono.data(), mono.size() * 4, cudaMemcpyHostToDevice);
         cudaMemcpy(d->ftw2, ftw2.data(), kLaneTwWords * 4, cudaMemcpyHostToDevice);
         cudaMemcpy(d->itw1, itw1.data(), kLaneTwWords * 4, cudaMemcpyHostToDevice);

@@ -189,13 +189,6 @@ static cudaError_t launch_br(const BrParams& P, int sm_count, cudaStream_t strea
 cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream) {
     return launch_br<4>(P, sm_count, stream);
 }
-// constant-memory tables that cannot be compile-time initialised (FP64 twiddle forms); once per device
-cudaError_t upload_constants() {
-    const UniformTw64 f = make_uniform64(false), i = make_uniform64(true);
-    cudaError_t e = cudaMemcpyToSymbol(c_tw64_fwd, &f, sizeof f);
-    if (e != cudaSuccess) return e;
-    return cudaMemcpyToSymbol(c_tw64_inv, &i, sizeof i);
-}
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream) {
     if (!P.jobs) return cudaSuccess;
     const u32 words = P.ks_stride >> 1;

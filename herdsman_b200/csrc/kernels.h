@@ -22,7 +22,6 @@ struct GatherParams {
 };
 
 cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream);
-cudaError_t upload_constants();      // call once per device before the first launch
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream);
 cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream);
 cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 polys, int sm_count, cudaStream_t stream);

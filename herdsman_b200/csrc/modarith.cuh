@@ -134,128 +134,3 @@ HERDB_HD u32 modswitch_qKS_to_q(u32 v) { return ((v + 8u) >> 4) & (kLweQ - 1); }
 struct alignas(16) V4 { u32 v[4]; };
 
 }  // namespace herdb
-
-// ================================================================================================
-// FP64-assisted modular multiplication.  On B200 IMAD.HI (and IMAD.WIDE) cost two issue slots of the
-// FMA pipe, so a Shoup product (IMAD.HI, IMAD, IMAD) occupies it for 4 slots.  The quotient can be
-// computed on the otherwise idle FP64 pipe instead: for y < 2^32 held in the low word of a register
-// pair whose high word is 0x43300000, the pair read as a double is exactly 2^52 + y, and
-//     fma(2^52 + y, c, 2^52 - 2^52*c) = 2^52 + y*c   (one rounding, to an integer since ulp = 1)
-// so the low word of the result is round(y*c).  With c = round(w/Q * 2^52) / 2^52 (2^52*c is an
-// integer, hence the addend is exact) that is round(w*y/Q) up to 2^-20, and
-//     r = w*y - q*Q  (two IMADs, mod 2^32)  is the SIGNED residue of w*y with |r| <= 0.51 Q.
-// Everything stays exact: r == w*y (mod Q); only its representative differs from Shoup's.
-namespace herdb {
-
-constexpr double kTwo52 = 4503599627370496.0;
-struct F64Tw { u32 w; u32 pad; double c; double k; };       // w, c = round(w/Q*2^52)/2^52, k = 2^52 - 2^52*c
-
-inline F64Tw make_f64tw(u32 w) {
-    F64Tw t;
-    t.w = w; t.pad = 0;
-    const unsigned __int128 num = ((unsigned __int128)w << 52);
-    const u64 ci = (u64)((num + kQ / 2) / kQ);               // round(w * 2^52 / Q), < 2^52
-    t.c = (double)ci / kTwo52;                                // exact: ci < 2^53
-    t.k = kTwo52 - (double)ci;                                // exact integer
-    return t;
-}
-
-HERDB_HD double pack52(u32 lo) {                              // the double 2^52 + lo
-#if defined(__CUDA_ARCH__)
-    return __hiloint2double(0x43300000, (int)lo);
-#else
-    u64 b = 0x4330000000000000ull | lo; double d; __builtin_memcpy(&d, &b, 8); return d;
-#endif
-}
-HERDB_HD u32 lo52(double d) {
-#if defined(__CUDA_ARCH__)
-    return (u32)__double2loint(d);
-#else
-    u64 b; __builtin_memcpy(&b, &d, 8); return (u32)b;
-#endif
-}
-HERDB_HD double fma64(double a, double b, double c) {
-#if defined(__CUDA_ARCH__)
-    return __fma_rn(a, b, c);
-#else
-    return __builtin_fma(a, b, c);
-#endif
-}
-// uniform-twiddle tables in the FP64 form (index = twiddle index 1..31 as in UniformTw)
-struct UniformTw64 { F64Tw v[32]; };
-inline UniformTw64 make_uniform64(bool inverse) {
-    UniformTw64 t;
-    t.v[0] = make_f64tw(1);
-    for (u32 k = 1; k < 32; ++k) t.v[k] = make_f64tw(inverse ? ctw_inv(k) : ctw_fwd(k));
-    return t;
-}
-#if defined(__CUDACC__)
-__constant__ UniformTw64 c_tw64_fwd;        // filled by upload_constants() (kernels.cu) once per device
-__constant__ UniformTw64 c_tw64_inv;
-#endif
-inline const UniformTw64& host_tw64(bool inverse) {
-    static const UniformTw64 f = make_uniform64(false), i = make_uniform64(true);
-    return inverse ? i : f;
-}
-#if defined(__CUDA_ARCH__)
-#define HERDB_TW64F(k) c_tw64_fwd.v[k]
-#define HERDB_TW64I(k) c_tw64_inv.v[k]
-#else
-#define HERDB_TW64F(k) host_tw64(false).v[k]
-#define HERDB_TW64I(k) host_tw64(true).v[k]
-#endif
-
-// signed residue of w*y (as u32 two's complement), |r| <= 0.51 Q, any y < 2^32
-HERDB_HD u32 mul_f64(u32 w, double c, double k, u32 y) {
-    const u32 q = lo52(fma64(pack52(y), c, k));
-    return w * y - q * kQ;
-}
-// the same without the per-twiddle addend: (2^52 + y) - 2^52 is exact, then fma(y, c, 2^52)
-HERDB_HD u32 mul_f64_2op(u32 w, double c, u32 y) {
-    const u32 q = lo52(fma64(pack52(y) - kTwo52, c, kTwo52));
-    return w * y - q * kQ;
-}
-
-}  // namespace herdb
-
-// ================================================================================================
-// FP64 quotient, modulus-2Q form (the one the blind-rotation kernel uses).  With c = ci / 2^52,
-// ci = round(w * 2^52 / 2Q) < 2^51, and Y = 2^52 + y (y < 2^32 in the low word of a register pair
-// whose high word is 0x43300000):
-//     fma(Y, c, 2^52) = 2^52 + ci + round(y*c)          (one rounding, ulp = 1, sum < 2^53)
-// so its low word is  low = lo32(ci) + q  (mod 2^32),  q = round(y*w/2Q) +- 2^-21, and
-//     r0 = w*y - low*2Q   (two IMADs, mod 2^32),   r0 + E == w*y - q*2Q,   E = lo32(ci)*2Q mod 2^32
-// is the SIGNED residue of w*y modulo 2Q (hence modulo Q), |r0 + E| <= Q + 128.  The addend of the
-// DFMA is the same for every twiddle, E rides on the butterfly's adds (a constant-bank operand for
-// lane-uniform twiddles).  Exactness never depends on the rounding; only the range bound does.
-namespace herdb {
-constexpr u32 kF64Slack = 128;                                // |r| <= Q + kF64Slack
-struct F64U { u32 w, E, nE, pad; double c; };                 // nE = -E mod 2^32
-inline F64U make_f64u(u32 w) {
-    F64U t;
-    const unsigned __int128 num = ((unsigned __int128)w << 52);
-    const u64 ci = (u64)((num + kQ) / (2ull * kQ));           // round(w * 2^52 / 2Q)
-    t.w = w; t.c = (double)ci / kTwo52;                       // exact (ci < 2^53)
-    t.E = (u32)ci * kQ2; t.nE = 0u - t.E; t.pad = 0;
-    return t;
-}
-HERDB_HD double with_lo(double d, u32 lo) {                   // replace the low word of a register pair
-#if defined(__CUDA_ARCH__)
-    return __hiloint2double(__double2hiint(d), (int)lo);
-#else
-    u64 b; __builtin_memcpy(&b, &d, 8); b = (b & 0xFFFFFFFF00000000ull) | lo; __builtin_memcpy(&d, &b, 8); return d;
-#endif
-}
-HERDB_HD double mk_double(u32 hi, u32 lo) {
-#if defined(__CUDA_ARCH__)
-    return __hiloint2double((int)hi, (int)lo);
-#else
-    u64 b = ((u64)hi << 32) | lo; double d; __builtin_memcpy(&d, &b, 8); return d;
-#endif
-}
-// r0 of the text: y in the low word of pair yd
-HERDB_HD u32 mul_q2(u32 w, double c, double yd) {
-    const u32 low = lo52(fma64(yd, c, kTwo52));
-    return w * lo52(yd) - low * kQ2;
-}
-}  // namespace herdb

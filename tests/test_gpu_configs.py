@@ -1,0 +1,103 @@
+"""GPU tests of the BASELINE.json configurations at STD128 (n = 512).  The oracle needs ~50 ms per gate per
+core, so full-size parity is replaced by size-independent properties: decrypt == plaintext evaluation on
+every row, bit-exact equality with the oracle on a few rows, and byte-identical outputs whichever way the
+rows are split across launches (the property row sharding over GPUs relies on)."""
+import numpy as np
+import pytest
+
+from herdsman_b200 import api, circuit as cm
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def backend():
+    b = api.Backend(devices=(0,))
+    yield b
+    b.close()
+
+
+@pytest.fixture(scope="module")
+def sess(backend, std128_key, oracle_lib):
+    backend.load_key_mem("cfg", std128_key["blob"])
+    return {"name": "cfg", "oracle": oracle_lib.Oracle(std128_key["blob"]), **std128_key}
+
+
+def _enc_words(s, cols, bits, seed):
+    mats = [cm.pack_words(c, b) for c, b in zip(cols, bits)]
+    return api.client_encrypt_bits(s["n"], s["sk"], np.concatenate(mats, axis=1), seed=seed)
+
+
+def test_config3_compare32_rows_and_split_invariance(backend, sess):
+    """configs[2]: x < y on two UINT32 columns; outputs do not depend on how rows are chunked"""
+    s = sess
+    c = cm.compare_circuit(32)
+    rows = 96
+    rng = np.random.default_rng(3)
+    x = rng.integers(0, 1 << 32, rows, dtype=np.uint64); y = rng.integers(0, 1 << 32, rows, dtype=np.uint64)
+    y[:8] = x[:8]                                      # equal operands: x < y is false
+    y[8:12] = x[8:12] + 1                              # differ in the lowest bit only (carry chain through all 32 levels)
+    rows_in = _enc_words(s, (x, y), (32, 32), seed=3)
+    out = backend.eval_circuit_rows(s["name"], c, rows_in)
+    assert out.shape == (rows, 1, s["n"] + 1)
+    dec = api.client_decrypt_bits(s["n"], s["sk"], out).reshape(rows)
+    assert np.array_equal(dec, (x < (y & 0xFFFFFFFF)).astype(dec.dtype))
+    # row sharding: two "devices" with contiguous slices give byte-identical rows
+    k = rows // 3
+    parts = np.concatenate([backend.eval_circuit_rows(s["name"], c, rows_in[:k]),
+                            backend.eval_circuit_rows(s["name"], c, rows_in[k:])])
+    assert np.array_equal(parts, out)
+    ref = s["oracle"].circuit_rows(c.to_c(), rows_in[10:12], c.out_bits)
+    assert np.array_equal(out[10:12], ref)
+
+
+def test_config4_multiply32_rows(backend, sess):
+    """configs[3]: 32-bit shift-and-add multiplier, 4,746 bootstraps per row over 181 levels"""
+    s = sess
+    c = cm.multiply_circuit(32)
+    info = api.analyze(c)
+    assert info["boot_gates"] > 4000 and info["levels"] > 100
+    rows = 6
+    x = np.array([0, 1, 0xFFFFFFFF, 0x80000001, 123456789, 0xDEADBEEF], np.uint64)
+    y = np.array([0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 3, 987654321, 0xCAFEBABE], np.uint64)
+    rows_in = _enc_words(s, (x, y), (32, 32), seed=4)
+    out = backend.eval_circuit_rows(s["name"], c, rows_in)
+    dec = cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out))
+    assert np.array_equal(dec.reshape(rows), (x * y) & 0xFFFFFFFF)
+
+
+def test_config5_pipeline_stages_equal_fused_plaintext(backend, sess):
+    """configs[4]: add -> compare -> select as three chained map stages on 8-bit columns"""
+    s = sess
+    rows = 40
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, rows, dtype=np.uint64); b = rng.integers(0, 256, rows, dtype=np.uint64)
+    d = rng.integers(0, 256, rows, dtype=np.uint64)
+    abd = _enc_words(s, (a, b, d), (8, 8, 8), seed=5)
+    w = s["n"] + 1
+    s1 = backend.eval_circuit_rows(s["name"], cm.adder_circuit(8), abd[:, :16])                     # a + b
+    s2 = backend.eval_circuit_rows(s["name"], cm.compare_circuit(8), np.concatenate([s1, abd[:, 16:]], axis=1))   # (a+b) < d
+    s3 = backend.eval_circuit_rows(s["name"], cm.select_circuit(8), np.concatenate([s2, s1, abd[:, 16:]], axis=1))
+    assert s3.shape == (rows, 8, w)
+    got = cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], s3)).reshape(rows)
+    sm = (a + b) % 256
+    assert np.array_equal(got, np.where(sm < d, sm, d))
+    # the fused single-stage circuit decrypts to the same plaintext
+    fused = backend.eval_circuit_rows(s["name"], cm.pipeline_circuit(8), abd)
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], fused)).reshape(rows), got)
+
+
+def test_config2_gate_batch_is_deterministic_and_order_free(backend, sess):
+    """configs[1]: a gate's output depends only on its own operands, not on batch position or batch size"""
+    s = sess
+    rng = np.random.default_rng(2)
+    B = 1500
+    a = rng.integers(0, 2, B).astype(np.uint8); b = rng.integers(0, 2, B).astype(np.uint8)
+    ca = api.client_encrypt_bits(s["n"], s["sk"], a, seed=2, first=0)
+    cb = api.client_encrypt_bits(s["n"], s["sk"], b, seed=2, first=1 << 22)
+    out = backend.eval_gate_batch(s["name"], "NAND", ca, cb)
+    perm = rng.permutation(B)
+    out_p = backend.eval_gate_batch(s["name"], "NAND", ca[perm], cb[perm])
+    assert np.array_equal(out_p, out[perm])
+    assert np.array_equal(backend.eval_gate_batch(s["name"], "NAND", ca[:7], cb[:7]), out[:7])
+    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))

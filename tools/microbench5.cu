@@ -2,7 +2,7 @@
 // with the three quotient forms; butterflies per clock per SM at 2 warps per scheduler (as in the kernel)
 #include <cstdio>
 #include <cuda_runtime.h>
-#include "../herdsman_b200/csrc/ntt_core.cuh"
+#include "experimental_ntt.cuh"
 using namespace herdb;
 struct UTw64 { F64Tw v[32]; };
 __constant__ UTw64 c_tw64;

@@ -6,7 +6,7 @@
 #include <cstdio>
 #include <vector>
 #include <cuda_runtime.h>
-#include "../herdsman_b200/csrc/ntt_core.cuh"
+#include "experimental_ntt.cuh"
 using namespace herdb;
 struct STw { int w[32]; int wp[32]; };
 __constant__ STw c_stw;
