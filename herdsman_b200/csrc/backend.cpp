@@ -161,7 +161,7 @@ int install_key_from_dev(herdb_ctx* ctx, Device& d, const char* session, const h
     CU(launch_bsk_convert(raw_bsk, k.bsk, d.ftw2, polys, d.sm_count, d.stream));
     CU(launch_ksk_relayout(raw_ksk, k.ksk, h.n, k.ks_stride, ks_rows, d.sm_count, d.stream));
     CU(cudaStreamSynchronize(d.stream));
-    d.stats.kernel_launches += 2;
+    d.stats.kernel_launches += 3;
     auto it = d.keys.find(session);
     if (it != d.keys.end()) { cudaFree(it->second.bsk); cudaFree(it->second.ksk); }
     d.keys[session] = k;

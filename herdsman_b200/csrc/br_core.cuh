@@ -10,13 +10,16 @@
 //
 // Data residency (per CTA, shared memory):
 //   acc  [kC][2][1024] u32   accumulator, NTT domain, pre-scaled by 1/N, canonical [0,Q)
-//   dig  [kC][8][1024] u32   NTT of the 8 signed-digit polynomials, lazy residues < 2^32
+//   dig  [kC][6][1024] u32   NTT of the signed-digit polynomials l = 0,1,2 of both components, lazy residues
+//                            < 2^32; the top digit l = 3 is never transformed (top-digit elimination,
+//                            modarith.cuh): its key rows are folded so that they multiply acc itself
 //   itw  [16][32][4]   u32   per-lane twiddles of the inverse pass 1
 //   lwe  [kC][n+1]     u16   prepared LWE ciphertext (ct1 + ct2 etc.)
-// Per step: phase A = one warp per (ciphertext, component): INTT, decompose, 4 forward NTTs;
-//           phase B = one thread per 4 evaluation points: 32 key words (128-bit loads from
-//           L2, shared by the 4 ciphertexts) x 8 digits multiply-accumulated exactly in 64
-//           bits, folded, multiplied by the two monomials and added into acc.
+// Per step: phase A = one warp per (ciphertext, component): INTT, decompose, 3 forward NTTs;
+//           phase B = one thread per 4 evaluation points: 32 key words (staged in shared memory by
+//           cp.async, shared by the 4 ciphertexts) x (6 digit transforms + the 2 accumulator components)
+//           multiply-accumulated exactly in 64 bits, folded, multiplied by the two monomials and added
+//           into acc.
 //
 // The body is templated on an execution environment so that tests/emu can run the very same
 // code on the CPU with host threads and barriers (there is no GPU in the build container).
@@ -44,7 +47,7 @@ struct GateDesc {
 struct Pool { u16* base; u32 row_cts; u32 pad; };    // ciphertext (r, idx) at base + (r*row_cts + idx)*(n+1)
 
 struct BrParams {
-    const u32* bsk;              // [n][2 sign][8 rows][2 cols][1024]  NTT domain, * 1/N, canonical
+    const u32* bsk;              // [n][2 sign][8 rows][2 cols][1024]  NTT domain, canonical, rows folded by fold_top_digit
     const u32* mono;             // [1024][1024]   NTT(X^(2*row) - 1), canonical
     const u32* ftw2;             // [16][32][4]    forward pass-2 lane twiddles
     const u32* itw1;             // [16][32][4]    inverse pass-1 lane twiddles
@@ -61,7 +64,7 @@ struct BrParams {
 template <int C>
 struct BrSmem {
     u32 acc[C][2][kN];
-    u32 dig[C][kDG2][kN];
+    u32 dig[C][2 * kDGT][kN];
     u32 itw[kLaneTwWords];       // inverse pass-1 lane twiddles
     u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (streamed by fwd_pass2_stream)
     u32 kst[2][4][kN];           // bootstrapping-key staging ring (cp.async): two digits x (sign, column) x 1024 points
@@ -181,9 +184,9 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             }
             env.syncwarp();                                   // all lanes done reading the scratch
 #pragma unroll
-            for (int l = 0; l < (int)kDG; ++l) {
+            for (int l = 0; l < (int)kDGT; ++l) {                // the top digit is not needed (top-digit elimination)
 #pragma unroll
-                for (int k = 0; k < 32; ++k) x[k] = (l == (int)kDG - 1) ? (d[k] >> (7 * l)) : ((d[k] >> (7 * l)) & 127u);
+                for (int k = 0; k < 32; ++k) x[k] = (d[k] >> (7 * l)) & 127u;
                 u32* out = S.dig[c][j + 2 * l];               // output polynomial index j + 2*l
                 fwd_pass1_digits(x);                          // raw digits r + 64; the offset is folded into stage 0
                 store_strided(out, lane, x);
@@ -205,7 +208,9 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                     for (int jo = 0; jo < 2; ++jo)
 #pragma unroll
                         for (int p = 0; p < 4; ++p) mac[c][s][jo][p] = 0;
-            // where digit r's key pieces live: r = 0,2,6 ring 0; r = 1,4 ring 1; r = 3,5,7 the consumed digit slots 0,1,2
+            // Row r = j + 2l of the key multiplies the transform of digit l of component j for l < 3 and, for
+            // l = 3 (r = 6, 7), the stored accumulator component j itself (folded rows, modarith.cuh).
+            // where row r's key pieces live: r = 0,2,6 ring 0; r = 1,4 ring 1; r = 3,5,7 the consumed digit slots 0,1,2
 #pragma unroll
             for (int r = 0; r < (int)kDG2; ++r) {
                 if (r == 0 || r == 1 || r == 2 || r == 4) env.cp_wait1();      // groups: {0} {1} | {2,3} | {4,5} | {6,7}
@@ -213,7 +218,8 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 const u32* kbase = (r == 0 || r == 2 || r == 6) ? &S.kst[0][0][phys_b]
                                  : (r == 1 || r == 4)           ? &S.kst[1][0][phys_b]
                                                                 : &S.dig[0][(r - 3) / 2][phys_b];
-                const u32 kstride = (r == 3 || r == 5 || r == 7) ? (u32)(kDG2 * kN) : kN;
+                constexpr u32 kDigCt = 2 * kDGT * kN;           // words between the digit blocks of two ciphertexts
+                const u32 kstride = (r == 3 || r == 5 || r == 7) ? kDigCt : kN;
                 V4 kv[2][2];
 #pragma unroll
                 for (int s = 0; s < 2; ++s)
@@ -222,7 +228,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 u32 dep = 0;
 #pragma unroll
                 for (int c = 0; c < kC; ++c) {
-                    V4 dv = *reinterpret_cast<const V4*>(&S.dig[c][r][phys_b]);
+                    V4 dv = *reinterpret_cast<const V4*>(r < 2 * (int)kDGT ? &S.dig[c][r][phys_b] : &S.acc[c][r - 2 * (int)kDGT][phys_b]);
                     dep |= dv.v[0];
 #pragma unroll
                     for (int s = 0; s < 2; ++s)
@@ -236,7 +242,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 if (r <= 2) {
                     env.cp_fence(dep ^ kv[1][1].v[0]);
                     stage_key(2 * r + 2, &S.kst[r & 1][0][phys_b], kN);
-                    stage_key(2 * r + 3, &S.dig[0][r][phys_b], kDG2 * kN);
+                    stage_key(2 * r + 3, &S.dig[0][r][phys_b], kDigCt);
                     env.cp_commit();
                 }
             }

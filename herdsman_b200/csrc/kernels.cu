@@ -5,6 +5,7 @@
 //   keyswitch_kernel      K4: LWE key switch (OpenFHE LWEEncryptionScheme::KeySwitch) + ModSwitch(qKS->q)
 //   gather_outputs_kernel OutputNode handling: copies / NOTs / constants into the output rows
 //   bsk_convert_kernel    key load: coefficient-domain RGSW rows -> NTT domain, * 1/N
+//   bsk_fold_kernel       key load: folds the gadget rows for the top-digit elimination
 //   ksk_relayout_kernel   key load: pads key-switch rows to a 16-byte multiple
 //   int_peak_kernel       measurement: raw IMAD / IADD3 / IMAD.HI / IMAD.WIDE issue rates
 //
@@ -134,6 +135,23 @@ __global__ void __launch_bounds__(256) bsk_convert_kernel(const u32* __restrict_
     }
 }
 
+// key load, second pass (in place): folds the four gadget rows of every (i, sign, component, column, point)
+// for the top-digit elimination (modarith.cuh, fold_top_digit)
+__global__ void __launch_bounds__(256) bsk_fold_kernel(u32* __restrict__ bsk, u32 n) {
+    const size_t total = (size_t)n * 2 * 2 * 2 * kN;                 // (i, sign, component j, column, point)
+    for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
+        const u32 x = (u32)(t % kN);
+        const u32 col = (u32)(t / kN) & 1u, j = (u32)(t / (2 * kN)) & 1u;
+        const size_t is = t / (4 * kN);                                // i * 2 + sign
+        u32 k[4];
+#pragma unroll
+        for (u32 l = 0; l < 4; ++l) k[l] = bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x];
+        fold_top_digit(k);
+#pragma unroll
+        for (u32 l = 0; l < 4; ++l) bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x] = k[l];
+    }
+}
+
 __global__ void ksk_relayout_kernel(const u16* __restrict__ in, u16* __restrict__ out, u32 n, u32 stride, size_t rows) {
     const size_t total = rows * stride;
     for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
@@ -205,6 +223,9 @@ cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStrea
 }
 cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 polys, int sm_count, cudaStream_t stream) {
     bsk_convert_kernel<<<sm_count * 2, 256, 0, stream>>>(in, out, ftw2, polys);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    bsk_fold_kernel<<<sm_count * 8, 256, 0, stream>>>(out, polys / (2 * kDG2 * 2));
     return cudaGetLastError();
 }
 cudaError_t launch_ksk_relayout(const u16* in, u16* out, u32 n, u32 stride, size_t rows, int sm_count, cudaStream_t stream) {

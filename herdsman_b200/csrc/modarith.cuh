@@ -63,6 +63,20 @@ static_assert(cmulmod(kNInv, kN) == 1, "N^-1");
 constexpr u32 ctw_fwd(u32 k) { return cpowmod(kPsi, cbitrev10(k)); }
 constexpr u32 ctw_inv(u32 k) { return cpowmod(kPsiInv, cbitrev10(k)); }
 
+// Top-digit elimination (br_core.cuh, "phase B"): the signed digits of a coefficient satisfy
+// t = r0 + B*r1 + B^2*r2 + B^3*r3 (mod Q), B = 2^7, so by linearity of the NTT
+//   NTT(r3) = B^-3 * (NTT(t) - NTT(r0) - B*NTT(r1) - B^2*NTT(r2))
+// and NTT(t) is the accumulator itself.  Substituting into sum_l NTT(r_l) * K_l gives the same element
+// of Z_Q from three digit transforms and the accumulator, against key rows folded once at load time:
+//   K'_l = K_l - B^(l-3) * K_3  (l = 0,1,2),   K'_3 = B^-3 * K_3 (multiplies the accumulator).
+constexpr u32 kBG = 1u << HERDB_BASEG_LOG;
+constexpr u32 kBGInv1 = cpowmod(kBG, kQ - 2);
+constexpr u32 kBGInv2 = cmulmod(kBGInv1, kBGInv1);
+constexpr u32 kBGInv3 = cmulmod(kBGInv2, kBGInv1);
+static_assert(cmulmod(kBGInv3, cmulmod(cmulmod(kBG, kBG), kBG)) == 1, "B^-3");
+static_assert(HERDB_DIGITS_G == 4, "top-digit elimination is written for 4 gadget digits");
+constexpr u32 kDGT = HERDB_DIGITS_G - 1;   // digit polynomials actually transformed per accumulator component
+
 // 2^31 mod Q and its Shoup companion: folds the high part of a 62-bit value
 constexpr u32 kR31 = (u32)((1ull << 31) % kQ);
 constexpr u32 kR31s = cshoup(kR31);
@@ -119,6 +133,19 @@ HERDB_HD u32 canon32(u32 x) { return csub(x - (x >> 27) * kQ, kQ); }
 HERDB_HD u32 fold62(u64 x) {
     u32 hi = (u32)(x >> 31), lo = (u32)x & 0x7FFFFFFFu;
     return mul_shoup_lazy(kR31, kR31s, hi) + lo;
+}
+// exact a*b mod Q for canonical a, b (key load only; 64-bit remainder)
+HERDB_HD u32 mulmod_slow(u32 a, u32 b) { return (u32)(((u64)a * b) % kQ); }
+// Folds the four gadget rows of one (LWE index, sign, accumulator component, column, evaluation point):
+// in  k[l] = K_l / N   (canonical; what the forward transform of the key load produces)
+// out k[l] = (K_l - B^(l-3) K_3) / N for l < 3,  k[3] = B^-3 * K_3  (NOT divided by N: it multiplies the
+//     stored accumulator, which already carries the 1/N)
+HERDB_HD void fold_top_digit(u32 (&k)[4]) {
+    const u32 t = k[3];
+    k[0] = csub(k[0] + kQ - mulmod_slow(t, kBGInv3), kQ);
+    k[1] = csub(k[1] + kQ - mulmod_slow(t, kBGInv2), kQ);
+    k[2] = csub(k[2] + kQ - mulmod_slow(t, kBGInv1), kQ);
+    k[3] = mulmod_slow(mulmod_slow(t, kN % kQ), kBGInv3);
 }
 // bank-conflict-free layout of a 1024-word polynomial in shared memory: word x lives at
 // swz(x); rows of 32 words, the 16-byte chunk index is XORed with the row index

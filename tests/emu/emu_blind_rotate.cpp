@@ -63,6 +63,15 @@ static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, cons
         ntt_forward_host(&bsk[p * kN]);
         for (u32 x = 0; x < kN; ++x) bsk[p * kN + x] = cmulmod(bsk[p * kN + x], kNInv);
     }
+    for (size_t is = 0; is < (size_t)n * 2; ++is)                       // fold the gadget rows (top-digit elimination)
+        for (u32 j = 0; j < 2; ++j)
+            for (u32 col = 0; col < 2; ++col)
+                for (u32 x = 0; x < kN; ++x) {
+                    u32 k[4];
+                    for (u32 l = 0; l < 4; ++l) k[l] = bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x];
+                    fold_top_digit(k);
+                    for (u32 l = 0; l < 4; ++l) bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x] = k[l];
+                }
     std::vector<u32> mono; build_monomial_table(mono);
     std::vector<u32> ftw2(kLaneTwWords), itw1(kLaneTwWords);
     build_lane_twiddles(ftw2.data(), itw1.data());
