@@ -68,6 +68,7 @@ struct BrSmem {
     u32 itw[kLaneTwWords];       // inverse pass-1 lane twiddles
     u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (streamed by fwd_pass2_stream)
     u32 kst[2][4][kN];           // bootstrapping-key staging ring (cp.async): two digits x (sign, column) x 1024 points
+    u32 mono[C][2][kN];          // the two monomial rows of this step per ciphertext (cp.async, land during phase A)
     u16 lwe[C][kLweMax + 8];
     u32 gate_b[C];               // prepared b and gate code per ciphertext
     u32 gate_code[C];
@@ -159,7 +160,17 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 #pragma unroll
                 for (int jo = 0; jo < 2; ++jo) env.cp16(dst0 + (2 * s + jo) * dst_stride, K + ((s * kDG2 + r) * 2 + jo) * kN);
         };
-        stage_key(0, &S.kst[0][0][phys_b], kN); env.cp_commit();
+        stage_key(0, &S.kst[0][0][phys_b], kN);
+        // monomial rows X^(+-a_i) - 1 of the four ciphertexts ride in the same group (consumed at the end of phase B)
+#pragma unroll
+        for (int cc = 0; cc < kC; ++cc) {
+            const u32 a = S.lwe[cc][i];
+            const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
+            const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
+            env.cp16(&S.mono[cc][0][phys_b], P.mono + (size_t)row_pos * kN + 4 * tid);
+            env.cp16(&S.mono[cc][1][phys_b], P.mono + (size_t)row_neg * kN + 4 * tid);
+        }
+        env.cp_commit();
         stage_key(1, &S.kst[1][0][phys_b], kN); env.cp_commit();
         // ===== phase A: warp = (ciphertext c, component j)
         {
@@ -183,18 +194,21 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 d[k] = (t < (kQ >> 1)) ? t + kB : t + (kB - kQ);
             }
             env.syncwarp();                                   // all lanes done reading the scratch
+            // digits l = 0,1,2 (the top digit is not needed: top-digit elimination), transformed together
+            u32 y[kDGT][32];
 #pragma unroll
-            for (int l = 0; l < (int)kDGT; ++l) {                // the top digit is not needed (top-digit elimination)
+            for (int l = 0; l < (int)kDGT; ++l)
 #pragma unroll
-                for (int k = 0; k < 32; ++k) x[k] = (d[k] >> (7 * l)) & 127u;
-                u32* out = S.dig[c][j + 2 * l];               // output polynomial index j + 2*l
-                fwd_pass1_digits(x);                          // raw digits r + 64; the offset is folded into stage 0
-                store_strided(out, lane, x);
-                env.syncwarp();
-                load_contig(out, lane, x);
-                fwd_pass2_stream(x, S.ftw, lane);            // lane twiddles streamed from smem: measured faster than
-                store_contig(out, lane, x);                   // holding 62 twiddle registers; < 22Q < 2^32, not reduced
-            }
+                for (int k = 0; k < 32; ++k) y[l][k] = (d[k] >> (7 * l)) & 127u;
+            fwd_pass1_digits_multi<(int)kDGT>(y);                 // raw digits r + 64; the offset is folded into stage 0
+#pragma unroll
+            for (int l = 0; l < (int)kDGT; ++l) store_strided(S.dig[c][j + 2 * l], lane, y[l]);   // output polynomial index j + 2*l
+            env.syncwarp();
+#pragma unroll
+            for (int l = 0; l < (int)kDGT; ++l) load_contig(S.dig[c][j + 2 * l], lane, y[l]);
+            fwd_pass2_stream_multi<(int)kDGT>(y, S.ftw, lane);   // lane twiddles streamed from smem, one load per 3 butterflies
+#pragma unroll
+            for (int l = 0; l < (int)kDGT; ++l) store_contig(S.dig[c][j + 2 * l], lane, y[l]);    // < 22Q < 2^32, not reduced
         }
         env.sync();
         // ===== phase B: thread = kChunks chunks of 4 evaluation points: 4*(tid + q*kThreads) ..+3
@@ -248,11 +262,8 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             }
 #pragma unroll
             for (int c = 0; c < kC; ++c) {
-                const u32 a = S.lwe[c][i];
-                const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
-                const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
-                V4 mp = env.ldg_v4(P.mono + (size_t)row_pos * kN + 4 * tid);
-                V4 mn = env.ldg_v4(P.mono + (size_t)row_neg * kN + 4 * tid);
+                const V4 mp = *reinterpret_cast<const V4*>(&S.mono[c][0][phys_b]);
+                const V4 mn = *reinterpret_cast<const V4*>(&S.mono[c][1][phys_b]);
 #pragma unroll
                 for (int jo = 0; jo < 2; ++jo) {
                     V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys_b]);

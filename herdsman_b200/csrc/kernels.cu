@@ -34,6 +34,7 @@ struct DevEnv {
     __device__ __forceinline__ void cp_commit() const { asm volatile("cp.async.commit_group;" ::: "memory"); }
     __device__ __forceinline__ void cp_wait1() const { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
     __device__ __forceinline__ void cp_wait0() const { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+    __device__ __forceinline__ void delay(u32 clocks) const { const long long t0 = clock64(); while (clock64() - t0 < (long long)clocks) { } }
     // orders the copies that follow after the shared-memory reads whose results feed `dep`
     __device__ __forceinline__ void cp_fence(u32 dep) const { asm volatile("" ::"r"(dep) : "memory"); }
 };

@@ -132,6 +132,61 @@ HERDB_HD void fwd_pass2_stream(u32 (&x)[32], const u32* lane_tw, u32 lane) {
     }
 }
 
+// M digit polynomials of the same accumulator component transformed together by one warp: M independent
+// butterflies per twiddle give the scheduler M times the instruction-level parallelism (a warp shares its
+// scheduler with only one other warp) and every streamed twiddle pair is loaded once for the M of them.
+template <int M>
+HERDB_HD void fwd_pass1_digits_multi(u32 (&x)[M][32]) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[m][k + 16]);
+            u32 u = x[m][k];
+            x[m][k] = u + v + kDigK1;
+            x[m][k + 16] = u - v + kDigK2;
+        }
+#pragma unroll
+    for (int s = 1; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[m][k + h]);
+                u32 u = x[m][k];
+                x[m][k] = u + v;
+                x[m][k + h] = u - v + kQ2;
+            }
+        }
+    }
+}
+template <int M>
+HERDB_HD void fwd_pass2_stream_multi(u32 (&x)[M][32], const u32* lane_tw, u32 lane) {
+    int off = 0;
+#pragma unroll
+    for (int s = 5; s < 10; ++s) {
+        const int t = 16 >> (s - 5);
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+            if (e & t) continue;
+            const int p = off + e / (2 * t);
+            const u32* tp = lane_tw + ((p >> 1) * 32 + lane) * 4 + (p & 1) * 2;
+            const u32 w = tp[0], wp = tp[1];
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                u32 v = mul_shoup_lazy(w, wp, x[m][e + t]);
+                u32 u = x[m][e];
+                x[m][e] = u + v;
+                x[m][e + t] = u - v + kQ2;
+            }
+        }
+        off += 16 / t;
+    }
+}
+
 // ---------------------------------------------------------------- inverse (GS): invariant all values in [0, 2Q)
 HERDB_HD void inv_pass1(u32 (&x)[32], const u32* lane_tw /* smem or global, chunked [g][32][4] */, u32 lane) {
     int off = 0;

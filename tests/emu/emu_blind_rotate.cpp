@@ -38,6 +38,7 @@ struct HostEnv {
     void cp_wait1() { complete(1); }
     void cp_wait0() { complete(0); }
     void cp_fence(u32) {}
+    void delay(u32) {}
 };
 
 template <int C> struct ThreadArg { HostEnv env; const BrParams* P; BrSmem<C>* S; u32 groups; };
