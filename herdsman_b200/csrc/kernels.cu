@@ -51,41 +51,50 @@ __global__ void __launch_bounds__(64 * C, 1) blind_rotate_kernel(const __grid_co
 
 // ------------------------------------------------------------------------------------------------
 // Key switch: a_out = -sum_{i,j} KSK_A[i][digit_j(a_i)][j], b_out = b - sum KSK_B[...]  (mod qKS),
-// then ModSwitch to q.  One CTA per job; thread w owns the u16 pair (2w, 2w+1) of the padded row.
-// Row sums are accumulated per 16-bit half in 32 bits (2048 rows * 2^14 < 2^25).
-__global__ void __launch_bounds__(288) keyswitch_kernel(const __grid_constant__ KsParams P) {
-    __shared__ u16 ext_s[kExtStride];
-    const u32 words = P.ks_stride >> 1;
-    const u32* ksk32 = reinterpret_cast<const u32*>(P.ksk);
+// then ModSwitch to q.  One CTA per job.  The 2N row numbers of the job are put in shared memory once;
+// thread w then owns the u16 quad (4w .. 4w+3) of the padded rows and sums them with 64-bit loads.  The
+// values are below 2^14, so a 32-bit word carries two independent 16-bit lanes: two rows are added per
+// step and the lanes masked back to 14 bits (only the sum mod qKS = 2^14 is needed), no unpacking.
+constexpr u32 kKsThreads = 160;
+__global__ void __launch_bounds__(kKsThreads) keyswitch_kernel(const __grid_constant__ KsParams P) {
+    __shared__ __align__(16) u32 row_s[2 * kN];
+    __shared__ u32 b_s;
+    static_assert(kDKS == 2 && kQKS == (1u << 14), "lane arithmetic below assumes two digits and qKS = 2^14");
+    const u32 quads = P.ks_stride >> 2;
+    const u32 w = threadIdx.x;
+    constexpr u32 kLaneMask = (kQKS - 1) | ((kQKS - 1) << 16);
     for (u32 job = blockIdx.x; job < P.jobs; job += gridDim.x) {
         __syncthreads();
-        for (u32 k = threadIdx.x; k < kExtStride / 2; k += blockDim.x)
-            reinterpret_cast<u32*>(ext_s)[k] = reinterpret_cast<const u32*>(P.ext + (size_t)job * kExtStride)[k];
+        const u16* ext = P.ext + (size_t)job * kExtStride;
+        for (u32 i = threadIdx.x; i < kN; i += blockDim.x) {
+            const u32 t = ext[i];
+            row_s[2 * i] = (i * kBaseKS + (t & (kBaseKS - 1))) * kDKS + 0;
+            row_s[2 * i + 1] = (i * kBaseKS + (t >> HERDB_BASEKS_LOG)) * kDKS + 1;
+        }
+        if (threadIdx.x == 0) b_s = ext[kN];
         __syncthreads();
-        const u32 w = threadIdx.x;
-        if (w < words) {
-            u32 lo = 0, hi = 0;
-#pragma unroll 8
-            for (u32 i = 0; i < kN; ++i) {
-                const u32 t = ext_s[i];
-                const u32 r0 = ((i * kBaseKS + (t & (kBaseKS - 1))) * kDKS + 0);
-                const u32 r1 = ((i * kBaseKS + (t >> HERDB_BASEKS_LOG)) * kDKS + 1);
-                const u32 w0 = __ldg(ksk32 + (size_t)r0 * words + w);
-                const u32 w1 = __ldg(ksk32 + (size_t)r1 * words + w);
-                lo += (w0 & 0xFFFFu) + (w1 & 0xFFFFu);
-                hi += (w0 >> 16) + (w1 >> 16);
+        if (w < quads) {
+            const uint2* base = reinterpret_cast<const uint2*>(P.ksk) + w;
+            u32 acc0 = 0, acc1 = 0;
+#pragma unroll 4
+            for (u32 k = 0; k < 2 * kN; k += 4) {
+                const uint4 r = *reinterpret_cast<const uint4*>(&row_s[k]);
+                const uint2 x0 = __ldg(base + (size_t)r.x * quads), x1 = __ldg(base + (size_t)r.y * quads);
+                const uint2 x2 = __ldg(base + (size_t)r.z * quads), x3 = __ldg(base + (size_t)r.w * quads);
+                acc0 = (acc0 + x0.x + x1.x) & kLaneMask; acc1 = (acc1 + x0.y + x1.y) & kLaneMask;
+                acc0 = (acc0 + x2.x + x3.x) & kLaneMask; acc1 = (acc1 + x2.y + x3.y) & kLaneMask;
             }
             const GateDesc g = P.gates[job / P.rows];
             const u32 row = job % P.rows;
             u16* out = P.pools[g.pool_out].base + ((size_t)row * P.pools[g.pool_out].row_cts + g.idx_out) * (P.n + 1);
-            const u32 k0 = 2 * w, k1 = 2 * w + 1;
-            if (k0 <= P.n) {
-                u32 v = (k0 == P.n ? (u32)ext_s[kN] - lo : 0u - lo) & (kQKS - 1);
-                out[k0] = (u16)modswitch_qKS_to_q(v);
-            }
-            if (k1 <= P.n) {
-                u32 v = (k1 == P.n ? (u32)ext_s[kN] - hi : 0u - hi) & (kQKS - 1);
-                out[k1] = (u16)modswitch_qKS_to_q(v);
+            const u32 sums[4] = {acc0 & 0xFFFFu, acc0 >> 16, acc1 & 0xFFFFu, acc1 >> 16};
+#pragma unroll
+            for (u32 e = 0; e < 4; ++e) {
+                const u32 k = 4 * w + e;
+                if (k <= P.n) {
+                    const u32 v = (k == P.n ? b_s - sums[e] : 0u - sums[e]) & (kQKS - 1);
+                    out[k] = (u16)modswitch_qKS_to_q(v);
+                }
             }
         }
     }
@@ -210,11 +219,10 @@ cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t st
 }
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream) {
     if (!P.jobs) return cudaSuccess;
-    const u32 words = P.ks_stride >> 1;
-    const u32 threads = ((words + 31) / 32) * 32;
-    const u32 max_grid = (u32)sm_count * 16;
+    if ((P.ks_stride & 3) || (P.ks_stride >> 2) > kKsThreads) return cudaErrorInvalidValue;
+    const u32 max_grid = (u32)sm_count * 12;                     // 12 resident CTAs of 160 threads per SM
     const u32 grid = P.jobs < max_grid ? P.jobs : max_grid;
-    keyswitch_kernel<<<grid, threads, 0, stream>>>(P);
+    keyswitch_kernel<<<grid, kKsThreads, 0, stream>>>(P);
     return cudaGetLastError();
 }
 cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream) {

@@ -1,0 +1,114 @@
+// tools/ntt_bench2.cu -- phase A of the blind-rotation step as the product kernel runs it today (inverse
+// NTT, signed digit decomposition, three forward NTTs transformed together, lane twiddles streamed from
+// shared memory), timed in isolation with 1, 2, 3 and 4 warps per scheduler.  Answers: how much of the
+// IMAD pipe can this code use as a function of occupancy?  (Warps beyond 8 alias the shared-memory
+// polynomials of warp % 8: the data is garbage, the instruction stream and its timing are the same.)
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o ntt_bench2 ntt_bench2.cu
+#include <cstdio>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../herdsman_b200/csrc/ntt_core.cuh"
+using namespace herdb;
+
+struct Smem {
+    u32 acc[4][2][kN];
+    u32 dig[4][2 * kDGT][kN];
+    u32 itw[kLaneTwWords];
+    u32 ftw[kLaneTwWords];
+};
+
+template <int WARPS, int REGCAP>
+__global__ void __launch_bounds__(WARPS * 32, 1) k(const u32* ftw_g, const u32* itw_g, u32* out, int iters) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    Smem& S = *reinterpret_cast<Smem*>(raw);
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = (tid >> 5) & 7;
+    for (u32 w = tid; w < kLaneTwWords; w += WARPS * 32) { S.itw[w] = itw_g[w]; S.ftw[w] = ftw_g[w]; }
+    for (u32 w = tid; w < 8 * kN; w += WARPS * 32) (&S.acc[0][0][0])[w] = (w * 2654435761u + blockIdx.x * 97u) % kQ;
+    __syncthreads();
+    const int c = warp >> 1, j = warp & 1;
+    for (int it = 0; it < iters; ++it) {
+        u32 x[32];
+        load_contig(S.acc[c][j], lane, x);
+        if (!(REGCAP & 2)) {
+            inv_pass1(x, S.itw, lane);
+            store_contig(S.dig[c][j], lane, x);
+            __syncwarp();
+            load_strided(S.dig[c][j], lane, x);
+            inv_pass2(x);
+        }
+        constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
+        u32 d[32];
+#pragma unroll
+        for (int kk = 0; kk < 32; ++kk) {
+            if (REGCAP & 4) { d[kk] = x[kk]; continue; }
+            u32 t = csub(x[kk], kQ);
+            d[kk] = (t < (kQ >> 1)) ? t + kB : t + (kB - kQ);
+        }
+        __syncwarp();
+        u32 y[kDGT][32];
+#pragma unroll
+        for (int l = 0; l < (int)kDGT; ++l)
+#pragma unroll
+            for (int kk = 0; kk < 32; ++kk) y[l][kk] = (d[kk] >> (7 * l)) & 127u;
+        fwd_pass1_digits_multi<(int)kDGT>(y);
+        if (!(REGCAP & 1)) {
+#pragma unroll
+            for (int l = 0; l < (int)kDGT; ++l) store_strided(S.dig[c][j + 2 * l], lane, y[l]);
+            __syncwarp();
+#pragma unroll
+            for (int l = 0; l < (int)kDGT; ++l) load_contig(S.dig[c][j + 2 * l], lane, y[l]);
+        }
+        fwd_pass2_stream_multi<(int)kDGT>(y, S.ftw, lane);
+#pragma unroll
+        for (int l = 0; l < (int)kDGT; ++l) store_contig(S.dig[c][j + 2 * l], lane, y[l]);
+        if (REGCAP & 8) continue;
+        __syncthreads();
+        if (it + 1 < iters) {          // next accumulator: some canonical values
+            u32 z[32];
+            load_contig(S.dig[c][j + 2], lane, z);
+#pragma unroll
+            for (int kk = 0; kk < 32; ++kk) z[kk] = canon32(z[kk]);
+            store_contig(S.acc[c][j], lane, z);
+        }
+        __syncthreads();
+    }
+    if (blockIdx.x == 0 && tid < 256)
+        for (u32 w = tid; w < 4 * 2 * kDGT * kN; w += 256) out[w] = canon32((&S.dig[0][0][0])[w]);
+}
+
+template <int WARPS, int REGCAP>
+void run(const u32* dftw, const u32* ditw, u32* dout, int sms) {
+    cudaFuncSetAttribute(k<WARPS, REGCAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    const int iters = 400;
+    k<WARPS, REGCAP><<<sms, WARPS * 32, sizeof(Smem)>>>(dftw, ditw, dout, 4); cudaDeviceSynchronize();
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a);
+    k<WARPS, REGCAP><<<sms, WARPS * 32, sizeof(Smem)>>>(dftw, ditw, dout, iters);
+    cudaEventRecord(b); cudaEventSynchronize(b);
+    float ms; cudaEventElapsedTime(&ms, a, b);
+    cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, k<WARPS, REGCAP>);
+    const double clk = ms * 1e-3 * 1.965e9 / iters;
+    const double pipe = (WARPS / 4.0) * ((REGCAP & 2) ? 3 : 4) * 160 * 8;            // warps per scheduler x 4 transforms x 160 warp-butterflies x 8 clocks
+    printf("mask %2d  %2d warps/SM (%d regs, %zu B local): %8.3f ms  %7.0f clk per phase A, butterfly pipe need %6.0f -> %.1f %%  [%s]\n", REGCAP, WARPS,
+           fa.numRegs, (size_t)fa.localSizeBytes, ms, clk, pipe, 100.0 * pipe / clk, cudaGetErrorString(cudaGetLastError()));
+}
+
+int main() {
+    std::vector<u32> ftw(kLaneTwWords), itw(kLaneTwWords);
+    build_lane_twiddles(ftw.data(), itw.data());
+    u32 *dftw, *ditw, *dout;
+    cudaMalloc(&dftw, ftw.size() * 4); cudaMalloc(&ditw, itw.size() * 4); cudaMalloc(&dout, 4 * 2 * kDGT * kN * 4);
+    cudaMemcpy(dftw, ftw.data(), ftw.size() * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(ditw, itw.data(), itw.size() * 4, cudaMemcpyHostToDevice);
+    int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    run<4, 0>(dftw, ditw, dout, sms);
+    run<8, 0>(dftw, ditw, dout, sms);
+    run<12, 0>(dftw, ditw, dout, sms);
+    run<16, 0>(dftw, ditw, dout, sms);
+    // ablations (bit 0: no transposition between the forward passes, 1: no inverse transform, 2: no decomposition
+    // arithmetic, 3: no barrier / refresh between iterations)
+    run<8, 8>(dftw, ditw, dout, sms); run<8, 9>(dftw, ditw, dout, sms); run<8, 10>(dftw, ditw, dout, sms); run<8, 12>(dftw, ditw, dout, sms);
+    run<8, 14>(dftw, ditw, dout, sms); run<8, 15>(dftw, ditw, dout, sms);
+    run<12, 8>(dftw, ditw, dout, sms); run<12, 15>(dftw, ditw, dout, sms);
+    return 0;
+}
