@@ -29,7 +29,7 @@ GATE = {"OR": 0, "AND": 1, "NOR": 2, "NAND": 3, "XOR_FAST": 4, "XNOR_FAST": 5}
 EXPORTS = [
     "herdb_create", "herdb_destroy", "herdb_strerror", "herdb_last_error", "herdb_device_count",
     "herdb_load_key", "herdb_load_key_mem", "herdb_load_key_dev", "herdb_unload_key", "herdb_key_lwe_n",
-    "herdb_map_async", "herdb_wait_idle", "herdb_partition_read", "herdb_partition_write", "herdb_partition_rows",
+    "herdb_map_async", "herdb_reduce_async", "herdb_reduce_rows", "herdb_wait_idle", "herdb_partition_read", "herdb_partition_write", "herdb_partition_rows",
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_client_key_blob_size", "herdb_client_keygen", "herdb_client_encrypt_bits", "herdb_client_decrypt_bits",
@@ -53,6 +53,10 @@ class herdb_stats(C.Structure):
 DONE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int)
 
 
+class herdb_input_frame(C.Structure):       # include/herdb.h: InputDataFramePtr of a ReduceTask
+    _fields_ = [("df_uuid", C.c_char_p), ("partition", C.c_uint32), ("row_count", C.c_uint64)]
+
+
 def lib():
     """Load libherdb.so; raises if the CUDA extension has not been built (no fallback)."""
     global _lib
@@ -73,6 +77,8 @@ def lib():
         L.herdb_unload_key.argtypes = [vp, cp]
         L.herdb_key_lwe_n.argtypes = [vp, cp, C.POINTER(u32)]
         L.herdb_map_async.argtypes = [vp, cp, cp, u32, u64, cp, u32, C.POINTER(herdb_circuit), DONE_FN, vp]
+        L.herdb_reduce_async.argtypes = [vp, cp, C.POINTER(herdb_input_frame), sz, cp, u32, C.POINTER(herdb_circuit), DONE_FN, vp]
+        L.herdb_reduce_rows.argtypes = [vp, cp, C.POINTER(herdb_circuit), vp, sz, vp]
         L.herdb_wait_idle.argtypes = [vp]
         L.herdb_partition_read.argtypes = [cp, u64, sz, vp]
         L.herdb_partition_write.argtypes = [cp, u64, sz, vp]
@@ -241,6 +247,15 @@ class Backend:
         self._check(self.L.herdb_eval_circuit_rows(self.h, session.encode(), C.byref(cc), _ptr(rows_in), _ptr(out), n_rows))
         return out
 
+    def reduce_rows(self, session, circuit: Circuit, rows_in):
+        """fold n rows (output-row layout) to one row with a binary reducer circuit (herdb_reduce_rows)"""
+        n = self.key_lwe_n(session)
+        rows_in = np.ascontiguousarray(rows_in)
+        out = np.empty((1, circuit.out_bits, n + 1), np.uint16)
+        cc = circuit.to_c()
+        self._check(self.L.herdb_reduce_rows(self.h, session.encode(), C.byref(cc), _ptr(rows_in), rows_in.shape[0], _ptr(out)))
+        return out
+
     def eval_circuit_rows_dev(self, session, circuit: Circuit, d_rows_in, d_rows_out, n_rows, device=0):
         cc = circuit.to_c()
         self._check(self.L.herdb_eval_circuit_rows_dev(self.h, session.encode(), device, C.byref(cc), _ptr(d_rows_in), _ptr(d_rows_out), n_rows))
@@ -291,6 +306,15 @@ class CryptoKeyPtr:            # crypto_key_ptr.hpp:10-13 (SchemaType::BINFHE ==
 class MapTask:                 # common/include/herd/common/model/worker/task.hpp:12-21
     session_uuid: str
     input_data_frame_ptr: InputDataFramePtr
+    output_data_frame_ptr: DataFramePtr
+    crypto_key_ptr: CryptoKeyPtr
+    circuit: Circuit
+
+
+@dataclasses.dataclass
+class ReduceTask:              # task.hpp:23-32
+    session_uuid: str
+    input_data_frame_ptrs: list
     output_data_frame_ptr: DataFramePtr
     crypto_key_ptr: CryptoKeyPtr
     circuit: Circuit
@@ -361,14 +385,24 @@ class CudaWorkerGroup:
 
     def schedule_task(self, task) -> TaskHandle:
         assert task is not None, "monostate task"           # grpc_worker_group.cpp:74
-        if not isinstance(task, MapTask):
-            raise NotImplementedError("ReduceTask is not on the hot path yet (SURVEY.md 8f N2)")
         h = TaskHandle()
         with self._lock:
             tag = self._next; self._next += 1
             self._handles[tag] = h
         cc = task.circuit.to_c()
         B = self.backend
+        if isinstance(task, ReduceTask):
+            frames = (herdb_input_frame * max(1, len(task.input_data_frame_ptrs)))()
+            for k, f in enumerate(task.input_data_frame_ptrs):
+                frames[k] = herdb_input_frame(f.pointer.uuid.encode(), f.pointer.partition, f.row_count)
+            rc = B.L.herdb_reduce_async(B.h, task.session_uuid.encode(), frames, len(task.input_data_frame_ptrs),
+                                        task.output_data_frame_ptr.uuid.encode(), task.output_data_frame_ptr.partition,
+                                        C.byref(cc), self._done, tag)
+            if rc:
+                with self._lock:
+                    self._handles.pop(tag, None)
+                h._mark_completed(TaskHandle.Status.ERROR)
+            return h
         rc = B.L.herdb_map_async(B.h, task.session_uuid.encode(),
                                  task.input_data_frame_ptr.pointer.uuid.encode(), task.input_data_frame_ptr.pointer.partition,
                                  task.input_data_frame_ptr.row_count,

@@ -245,6 +245,24 @@ def pipeline_circuit(bits=8, basis="wire"):
     return c
 
 
+def reduce_add_circuit(bits=8, basis="wire"):
+    """binary reducer of a ReduceStage (stage.hpp:29-34): two rows of one UINT<bits> column -> their sum mod 2^bits"""
+    t = {8: DataType.UINT8, 16: DataType.UINT16, 32: DataType.UINT32, 64: DataType.UINT64}[bits]
+    c = Circuit([[t], [t]], [("sum", t)])
+    c.output_word(0, _ripple_add(c, c.input_word(0, 0), c.input_word(1, 0), basis))
+    return c
+
+
+def reduce_max_circuit(bits=8, basis="wire"):
+    """binary reducer: two rows of one UINT<bits> column -> the larger value"""
+    t = {8: DataType.UINT8, 16: DataType.UINT16, 32: DataType.UINT32, 64: DataType.UINT64}[bits]
+    c = Circuit([[t], [t]], [("max", t)])
+    xs, ys = c.input_word(0, 0), c.input_word(1, 0)
+    lt = _less_than(c, xs, ys, basis)
+    c.output_word(0, [c.or_(c.and_(lt, y), c.and_(c.not_(lt), x)) for x, y in zip(xs, ys)])
+    return c
+
+
 def single_gate_circuit(op=Operation.NAND):
     """config 2 as a circuit: (BIT, BIT) -> BIT."""
     c = Circuit([[DataType.BIT, DataType.BIT]], [("o", DataType.BIT)])

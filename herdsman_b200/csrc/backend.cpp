@@ -540,14 +540,11 @@ int write_partition(herdb_ctx* ctx, const std::string& path, uint64_t row_count,
     return rc;
 }
 
+int session_lwe_n(herdb_ctx* ctx, const std::string& session, uint32_t* n);
+
 int run_map_task(herdb_ctx* ctx, const MapTaskReq& t) {
     uint32_t n = 0;
-    int rc = herdb_key_lwe_n(ctx, t.session.c_str(), &n);
-    if (rc == HERDB_ERR_NOKEY) {                       // first task of a session: pull the key from <key_dir>
-        rc = herdb_load_key(ctx, t.session.c_str(), 1 /* SchemaType::BINFHE, schema_type.hpp:9-13 */);
-        if (rc) return rc;
-        rc = herdb_key_lwe_n(ctx, t.session.c_str(), &n);
-    }
+    int rc = session_lwe_n(ctx, t.session, &n);
     if (rc) return rc;
     const size_t w = n + 1;
     std::vector<uint16_t> rows_in, rows_out;
@@ -561,7 +558,84 @@ int run_map_task(herdb_ctx* ctx, const MapTaskReq& t) {
     return write_partition(ctx, partition_path(ctx, t.session, t.out_df, t.out_part), t.row_count, t.circuit.out_bits * w * 2, rows_out);
 }
 
+// a reduce circuit takes two rows of the output layout: inputs[0] == inputs[1] == output column types
+int check_reduce_circuit(herdb_ctx* ctx, const herdb_circuit* c) {
+    bool ok = c->n_tuples == 2;
+    if (ok) {
+        const u32 f0 = c->in_tuple_offsets[1] - c->in_tuple_offsets[0], f1 = c->in_tuple_offsets[2] - c->in_tuple_offsets[1];
+        ok = f0 == f1 && f0 == c->n_out_fields;
+        for (u32 f = 0; ok && f < f0; ++f)
+            ok = c->in_field_types[c->in_tuple_offsets[0] + f] == c->out_field_types[f] &&
+                 c->in_field_types[c->in_tuple_offsets[1] + f] == c->out_field_types[f];
+    }
+    if (!ok) ctx->set_error("reduce circuit: needs two input tuples with the column types of the output");
+    return ok ? HERDB_OK : HERDB_ERR_ARG;
+}
+
+// balanced pairwise fold of `m` rows (out-row layout, contiguous) to one row; every round is one batched
+// evaluation: rows 2i and 2i+1 are adjacent in memory, i.e. already the concatenated input row of pair i
+int reduce_rows_host(herdb_ctx* ctx, const char* session, const CompiledCircuit& cc, std::vector<uint16_t>& cur, size_t m, size_t w) {
+    const size_t row = (size_t)cc.out_bits * w;
+    std::vector<uint16_t> next;
+    while (m > 1) {
+        const size_t pairs = m / 2, odd = m & 1;
+        next.resize((pairs + odd) * row);
+        int rc = eval_rows_host(ctx, session, cc, cur.data(), next.data(), pairs);
+        if (rc) return rc;
+        if (odd) memcpy(next.data() + pairs * row, cur.data() + (m - 1) * row, row * 2);
+        cur.swap(next);
+        m = pairs + odd;
+    }
+    cur.resize(row);
+    return HERDB_OK;
+}
+
+int session_lwe_n(herdb_ctx* ctx, const std::string& session, uint32_t* n) {
+    int rc = herdb_key_lwe_n(ctx, session.c_str(), n);
+    if (rc == HERDB_ERR_NOKEY) {                       // first task of a session: pull the key from <key_dir>
+        rc = herdb_load_key(ctx, session.c_str(), 1 /* SchemaType::BINFHE, schema_type.hpp:9-13 */);
+        if (rc) return rc;
+        rc = herdb_key_lwe_n(ctx, session.c_str(), n);
+    }
+    return rc;
+}
+
+int run_reduce_task(herdb_ctx* ctx, const MapTaskReq& t) {
+    uint32_t n = 0;
+    int rc = session_lwe_n(ctx, t.session, &n);
+    if (rc) return rc;
+    const size_t w = n + 1, row_bytes = (size_t)t.circuit.out_bits * w * 2;
+    std::vector<uint16_t> rows, part;
+    size_t m = 0;
+    for (const InFrame& f : t.inputs) {
+        rc = read_partition(ctx, partition_path(ctx, t.session, f.df, f.part), f.row_count, row_bytes, part);
+        if (rc) return rc;
+        rows.insert(rows.end(), part.begin(), part.end());
+        m += f.row_count;
+    }
+    if (!m) { ctx->set_error("reduce task without input rows"); return HERDB_ERR_ARG; }
+    rc = reduce_rows_host(ctx, t.session.c_str(), t.circuit, rows, m, w);
+    if (rc) return rc;
+    return write_partition(ctx, partition_path(ctx, t.session, t.out_df, t.out_part), 1, row_bytes, rows);
+}
+
 }  // namespace
+
+extern "C" int herdb_reduce_rows(herdb_ctx* ctx, const char* session, const herdb_circuit* circuit,
+                                 const uint16_t* rows_in, size_t n_rows, uint16_t* row_out) {
+    if (!ctx || !session || !circuit || !rows_in || !row_out || !n_rows) return HERDB_ERR_ARG;
+    CompiledCircuit cc; std::string err;
+    int rc = compile_circuit(circuit, cc, err);
+    if (rc) { ctx->set_error("circuit: " + err); return rc; }
+    rc = check_reduce_circuit(ctx, circuit); if (rc) return rc;
+    uint32_t n = 0;
+    rc = herdb_key_lwe_n(ctx, session, &n); if (rc) return rc;
+    const size_t w = n + 1, row = (size_t)cc.out_bits * w;
+    std::vector<uint16_t> cur(rows_in, rows_in + n_rows * row);
+    rc = reduce_rows_host(ctx, session, cc, cur, n_rows, w); if (rc) return rc;
+    memcpy(row_out, cur.data(), row * 2);
+    return HERDB_OK;
+}
 
 extern "C" int herdb_partition_read(const char* path, uint64_t row_count, size_t row_bytes, void* rows_out) {
     if (!path || (!rows_out && row_count && row_bytes)) return HERDB_ERR_ARG;
@@ -611,7 +685,7 @@ static void worker_loop(herdb_ctx* ctx) {
             ctx->queue.pop_front();
             ctx->in_flight++;
         }
-        const int rc = run_map_task(ctx, t);
+        const int rc = t.reduce ? run_reduce_task(ctx, t) : run_map_task(ctx, t);
         // CUDA / IO / format errors => ERROR (job fails, executor.cpp:168-178); TIME_OUT is never produced
         if (t.done) t.done(t.user, rc == HERDB_OK ? HERDB_TASK_COMPLETED : HERDB_TASK_ERROR);
         {
@@ -631,6 +705,28 @@ extern "C" int herdb_map_async(herdb_ctx* ctx, const char* session, const char* 
     if (rc) { ctx->set_error("circuit: " + err); return rc; }
     t.session = session; t.in_df = in_df; t.out_df = out_df; t.in_part = in_part; t.out_part = out_part;
     t.row_count = row_count; t.done = done; t.user = user;
+    {
+        std::lock_guard<std::mutex> l(ctx->q_mu);
+        if (ctx->stop) return HERDB_ERR_ARG;
+        ctx->queue.push_back(std::move(t));
+    }
+    ctx->q_cv.notify_one();
+    return HERDB_OK;
+}
+
+extern "C" int herdb_reduce_async(herdb_ctx* ctx, const char* session, const herdb_input_frame* inputs, size_t n_inputs,
+                                  const char* out_df, uint32_t out_part, const herdb_circuit* circuit, herdb_done_fn done, void* user) {
+    if (!ctx || !session || (!inputs && n_inputs) || !out_df || !circuit) return HERDB_ERR_ARG;
+    MapTaskReq t;
+    std::string err;
+    int rc = compile_circuit(circuit, t.circuit, err);
+    if (rc) { ctx->set_error("circuit: " + err); return rc; }
+    rc = check_reduce_circuit(ctx, circuit); if (rc) return rc;
+    t.reduce = true; t.session = session; t.out_df = out_df; t.out_part = out_part; t.done = done; t.user = user;
+    for (size_t k = 0; k < n_inputs; ++k) {
+        if (!inputs[k].df_uuid) return HERDB_ERR_ARG;
+        t.inputs.push_back(InFrame{inputs[k].df_uuid, inputs[k].partition, inputs[k].row_count});
+    }
     {
         std::lock_guard<std::mutex> l(ctx->q_mu);
         if (ctx->stop) return HERDB_ERR_ARG;

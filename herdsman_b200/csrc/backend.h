@@ -46,10 +46,13 @@ struct Device {
     std::mutex mu;               // one host thread drives a device at a time
 };
 
-struct MapTaskReq {
+struct InFrame { std::string df; u32 part = 0; uint64_t row_count = 0; };
+struct MapTaskReq {                                  // a MapTask, or a ReduceTask when `reduce` is set
     std::string session, in_df, out_df;
     u32 in_part = 0, out_part = 0;
     uint64_t row_count = 0;
+    bool reduce = false;
+    std::vector<InFrame> inputs;                     // ReduceTask::input_data_frame_ptrs
     CompiledCircuit circuit;
     herdb_done_fn done = nullptr;
     void* user = nullptr;

@@ -1,5 +1,5 @@
 // cuda_worker_group.hpp -- the reference-side binding: an IWorkerGroup that hands herdsman's
-// MapTask to the B200 backend through the C ABI of include/herdb.h.
+// MapTask / ReduceTask to the B200 backend through the C ABI of include/herdb.h.
 //
 // This header is compiled INSIDE herdsman (C++20), next to GrpcWorkerGroup / LambdaWorkerGroup:
 //   implements   IWorkerGroup                 include/execution/worker/i_worker_group.hpp:12-49
@@ -72,19 +72,35 @@ public:
 	{
 		assert(!std::holds_alternative<std::monostate>(task));          // grpc_worker_group.cpp:74
 		auto handle = std::make_shared<CudaTaskHandle>();
-		if(!std::holds_alternative<herd::common::MapTask>(task))
-		{
-			fail_later(handle);                                          // ReduceTask: SURVEY.md 8f N2
-			return handle;
-		}
-		const auto& map_task = std::get<herd::common::MapTask>(task);
-		Flat flat = flatten(map_task.circuit);
-
 		auto* pending = new Pending{this, handle};
 		{
 			std::unique_lock lock(pending_mutex_);
 			pending_[pending] = handle;                                  // keeps the handle alive (grpc_worker_group.cpp:100)
 		}
+		if(std::holds_alternative<herd::common::ReduceTask>(task))       // task.hpp:23-32
+		{
+			const auto& reduce_task = std::get<herd::common::ReduceTask>(task);
+			Flat flat = flatten(reduce_task.circuit);
+			std::vector<std::string> uuids;
+			std::vector<herdb_input_frame> frames;
+			uuids.reserve(reduce_task.input_data_frame_ptrs.size());
+			for(const auto& ptr: reduce_task.input_data_frame_ptrs)
+			{
+				uuids.emplace_back(ptr.pointer.uuid.as_string());
+				frames.push_back(herdb_input_frame{uuids.back().c_str(), ptr.pointer.partition, ptr.row_count});
+			}
+			const int rc = herdb_reduce_async(
+					ctx_, reduce_task.session_uuid.as_string().c_str(), frames.data(), frames.size(),
+					reduce_task.output_data_frame_ptr.uuid.as_string().c_str(), reduce_task.output_data_frame_ptr.partition,
+					&flat.circuit, &CudaWorkerGroup::on_done, pending);
+			if(rc != HERDB_OK)
+			{
+				refuse(pending, handle);
+			}
+			return handle;
+		}
+		const auto& map_task = std::get<herd::common::MapTask>(task);
+		Flat flat = flatten(map_task.circuit);
 		const int rc = herdb_map_async(
 				ctx_, map_task.session_uuid.as_string().c_str(),
 				map_task.input_data_frame_ptr.pointer.uuid.as_string().c_str(), map_task.input_data_frame_ptr.pointer.partition,
@@ -93,18 +109,24 @@ public:
 				&flat.circuit, &CudaWorkerGroup::on_done, pending);
 		if(rc != HERDB_OK)
 		{
-			{
-				std::unique_lock lock(pending_mutex_);
-				pending_.erase(pending);
-			}
-			delete pending;
-			fail_later(handle);
+			refuse(pending, handle);
 		}
 		return handle;
 	}
 
 private:
 	struct Pending { CudaWorkerGroup* group; std::shared_ptr<CudaTaskHandle> handle; };
+
+	// the backend refused the task synchronously (malformed circuit, ...): ERROR, but not from inside schedule_task
+	void refuse(Pending* pending, const std::shared_ptr<CudaTaskHandle>& handle)
+	{
+		{
+			std::unique_lock lock(pending_mutex_);
+			pending_.erase(pending);
+		}
+		delete pending;
+		fail_later(handle);
+	}
 	struct Flat
 	{
 		std::vector<herdb_node> nodes;

@@ -131,6 +131,26 @@ int herdb_map_async(herdb_ctx* ctx, const char* session_uuid,
                     const char* in_df_uuid, uint32_t in_partition, uint64_t row_count,
                     const char* out_df_uuid, uint32_t out_partition,
                     const herdb_circuit* circuit, herdb_done_fn done, void* user);
+/* == IWorkerGroup::schedule_task(ReduceTask) (task.hpp:23-32, worker.proto:39-48; built at
+ * execution_service.cpp:474-513).  The rows of all input partitions, in the order given, are folded to ONE
+ * output row with the binary circuit: inputs[0] and inputs[1] are two rows of the same column layout as
+ * the output (InputNode::tuple_index selects which, nodes.hpp:12-21).  The reference worker is not in the
+ * tree, so the folding order is this backend's own [INFERRED]: a balanced pairwise tree, round by round
+ * over the current list (0,1),(2,3),...; an odd last row is carried unchanged to the end of the next
+ * list.  Every round is one batched evaluation of the circuit over all pairs (the same level-batched
+ * kernels as a map task).  The output partition receives exactly one row. */
+typedef struct herdb_input_frame {
+    const char* df_uuid;          /* InputDataFramePtr.pointer.uuid      (data_frame_ptr.hpp:15-19) */
+    uint32_t    partition;        /* InputDataFramePtr.pointer.partition                            */
+    uint64_t    row_count;        /* InputDataFramePtr.row_count                                    */
+} herdb_input_frame;
+int herdb_reduce_async(herdb_ctx* ctx, const char* session_uuid,
+                       const herdb_input_frame* inputs, size_t n_inputs,
+                       const char* out_df_uuid, uint32_t out_partition,
+                       const herdb_circuit* circuit, herdb_done_fn done, void* user);
+/* the same fold over host rows (n_rows >= 1 rows of out-row layout in, one row out) */
+int herdb_reduce_rows(herdb_ctx* ctx, const char* session_uuid, const herdb_circuit* circuit,
+                      const uint16_t* rows_in, size_t n_rows, uint16_t* row_out);
 /* blocks until every task scheduled so far has completed */
 int herdb_wait_idle(herdb_ctx* ctx);
 /* Partition-file framing used by the task path (host only, no device needed):

@@ -48,6 +48,8 @@ BUILDERS = [
     ("lt32", lambda b: cm.compare_circuit(32, b), 2, lambda v: (v[0] < v[1]).astype(np.uint64), 32),
     ("mul8", lambda b: cm.multiply_circuit(8, b), 2, lambda v: (v[0] * v[1]) % 256, 8),
     ("mul16", lambda b: cm.multiply_circuit(16, b), 2, lambda v: (v[0] * v[1]) % 65536, 16),
+    ("radd8", lambda b: cm.reduce_add_circuit(8, b), 2, lambda v: (v[0] + v[1]) % 256, 8),
+    ("rmax8", lambda b: cm.reduce_max_circuit(8, b), 2, lambda v: np.maximum(v[0], v[1]), 8),
     ("pipe8", lambda b: cm.pipeline_circuit(8, b), 3, lambda v: np.where((v[0] + v[1]) % 256 < v[2], (v[0] + v[1]) % 256, v[2]), 8),
 ]
 

@@ -118,3 +118,51 @@ def test_empty_partition_and_error_statuses(world):
     # malformed circuit is refused at schedule time and reported through the handle
     broken = cm.Circuit([[cm.DataType.BIT]], [("o", cm.DataType.BIT)]); broken.output_bit(0, 0, broken.input(0, 5, 0))
     assert w["wg"].schedule_task(_task(w, broken, df2, out_df, 0, 2)).wait(120) == api.TaskHandle.Status.ERROR
+
+
+def _oracle_tree_fold(orc, c, rows):
+    """the backend's documented folding order (include/herdb.h, herdb_reduce_async) restated with the oracle:
+    pairs (0,1),(2,3),... per round, an odd last row carried to the end of the next list"""
+    cur = rows
+    while cur.shape[0] > 1:
+        m = cur.shape[0]
+        pairs = cur[:m - (m & 1)].reshape(m // 2, 2 * cur.shape[1], cur.shape[2])
+        nxt = orc.circuit_rows(c.to_c(), pairs, c.out_bits)
+        cur = np.concatenate([nxt, cur[m - 1:]]) if m & 1 else nxt
+    return cur
+
+
+def test_reduce_task_over_partitions_matches_oracle(world):
+    """IWorkerGroup::schedule_task(ReduceTask): rows of several input partitions folded to one output row"""
+    w = world
+    c = cm.reduce_add_circuit(8)
+    n_rows, parts = 7, 3                                         # 3 + 2 + 2 rows, odd counts in the tree
+    vals = np.random.default_rng(5).integers(0, 256, n_rows)
+    rows = api.client_encrypt_bits(w["n"], w["sk"], cm.pack_words(vals, 8), seed=43)
+    in_df = _frame(w, rows, parts)
+    out_df = str(uuid.uuid4()); (w["storage"] / w["session"] / out_df).mkdir(parents=True)
+    ptrs = [api.InputDataFramePtr(api.DataFramePtr(in_df, k), api.partition_rows(n_rows, parts, k)) for k in range(parts)]
+    task = api.ReduceTask(w["session"], ptrs, api.DataFramePtr(out_df, 0), api.CryptoKeyPtr(1), c)
+    assert w["wg"].schedule_task(task).wait(300) == api.TaskHandle.Status.COMPLETED
+    got = api.partition_read(w["storage"] / w["session"] / out_df / "0", 1, 8, w["n"])
+    assert cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got))[0] == vals.sum() % 256
+    assert np.array_equal(got, _oracle_tree_fold(w["oracle"], c, rows))           # bit-exact, same folding order
+    # a single input row passes through unchanged; a map-shaped circuit is refused
+    one = _frame(w, rows[:1], 1)
+    t1 = api.ReduceTask(w["session"], [api.InputDataFramePtr(api.DataFramePtr(one, 0), 1)], api.DataFramePtr(out_df, 1), api.CryptoKeyPtr(1), c)
+    assert w["wg"].schedule_task(t1).wait(120) == api.TaskHandle.Status.COMPLETED
+    assert np.array_equal(api.partition_read(w["storage"] / w["session"] / out_df / "1", 1, 8, w["n"]), rows[:1])
+    bad = api.ReduceTask(w["session"], ptrs, api.DataFramePtr(out_df, 2), api.CryptoKeyPtr(1), cm.adder_circuit(8))
+    assert w["wg"].schedule_task(bad).wait(120) == api.TaskHandle.Status.ERROR
+    none = api.ReduceTask(w["session"], [], api.DataFramePtr(out_df, 3), api.CryptoKeyPtr(1), c)
+    assert w["wg"].schedule_task(none).wait(120) == api.TaskHandle.Status.ERROR
+
+
+def test_reduce_rows_max(world):
+    w = world
+    c = cm.reduce_max_circuit(8)
+    vals = np.random.default_rng(6).integers(0, 256, 6)
+    rows = api.client_encrypt_bits(w["n"], w["sk"], cm.pack_words(vals, 8), seed=44)
+    got = w["wg"].backend.reduce_rows(w["session"], c, rows)
+    assert cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got))[0] == vals.max()
+    assert np.array_equal(got, _oracle_tree_fold(w["oracle"], c, rows))
