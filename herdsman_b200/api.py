@@ -30,7 +30,7 @@ EXPORTS = [
     "herdb_create", "herdb_destroy", "herdb_strerror", "herdb_last_error", "herdb_device_count",
     "herdb_load_key", "herdb_load_key_mem", "herdb_load_key_dev", "herdb_unload_key", "herdb_key_lwe_n",
     "herdb_map_async", "herdb_reduce_async", "herdb_reduce_rows", "herdb_wait_idle", "herdb_partition_read", "herdb_partition_write", "herdb_partition_rows",
-    "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
+    "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_pipeline_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_client_key_blob_size", "herdb_client_keygen", "herdb_client_encrypt_bits", "herdb_client_decrypt_bits",
 ]
@@ -86,6 +86,7 @@ def lib():
         L.herdb_eval_gate_batch.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz]
         L.herdb_eval_gate_batch_dev.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz]
         L.herdb_eval_circuit_rows.argtypes = [vp, cp, C.POINTER(herdb_circuit), vp, vp, sz]
+        L.herdb_eval_pipeline_rows.argtypes = [vp, cp, C.POINTER(C.POINTER(herdb_circuit)), sz, vp, vp, sz]
         L.herdb_eval_circuit_rows_dev.argtypes = [vp, cp, ci, C.POINTER(herdb_circuit), vp, vp, sz]
         L.herdb_circuit_analyze.argtypes = [C.POINTER(herdb_circuit), C.POINTER(herdb_circuit_info)]
         L.herdb_get_stats.argtypes = [vp, ci, C.POINTER(herdb_stats)]
@@ -245,6 +246,16 @@ class Backend:
             out = np.empty((n_rows, circuit.out_bits, n + 1), np.uint16)
         cc = circuit.to_c()
         self._check(self.L.herdb_eval_circuit_rows(self.h, session.encode(), C.byref(cc), _ptr(rows_in), _ptr(out), n_rows))
+        return out
+
+    def eval_pipeline_rows(self, session, circuits, rows_in):
+        """chained map stages, intermediates resident in HBM (herdb_eval_pipeline_rows)"""
+        n = self.key_lwe_n(session)
+        rows_in = np.ascontiguousarray(rows_in)
+        out = np.empty((rows_in.shape[0], circuits[-1].out_bits, n + 1), np.uint16)
+        ccs = [c.to_c() for c in circuits]
+        arr = (C.POINTER(herdb_circuit) * len(ccs))(*[C.pointer(c) for c in ccs])
+        self._check(self.L.herdb_eval_pipeline_rows(self.h, session.encode(), arr, len(ccs), _ptr(rows_in), _ptr(out), rows_in.shape[0]))
         return out
 
     def reduce_rows(self, session, circuit: Circuit, rows_in):

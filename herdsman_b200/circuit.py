@@ -47,7 +47,7 @@ class NodeKind(enum.IntEnum):
 
 
 class herdb_node(C.Structure):
-    _fields_ = [("kind", C.c_uint8), ("op", C.c_uint8), ("const_val", C.c_uint8), ("reserved", C.c_uint8),
+    _fields_ = [("kind", C.c_uint8), ("op", C.c_uint8), ("const_val", C.c_uint8), ("flags", C.c_uint8),
                 ("tuple", C.c_uint32), ("field", C.c_uint32), ("bit", C.c_uint32)]
 
 
@@ -79,8 +79,8 @@ class Circuit:
         self._keep = None
 
     # -- graph construction (DAG::emplace / add_edge) ------------------------------------------
-    def _add(self, kind, op=0, const=0, tup=0, field=0, bit=0, parents=()):
-        self.nodes.append((int(kind), int(op), int(const), int(tup), int(field), int(bit)))
+    def _add(self, kind, op=0, const=0, tup=0, field=0, bit=0, parents=(), flags=0):
+        self.nodes.append((int(kind), int(op), int(const), int(tup), int(field), int(bit), int(flags)))
         nid = len(self.nodes) - 1
         for p in parents:
             self.edges.append((int(p), nid))
@@ -92,8 +92,8 @@ class Circuit:
     def constant(self, value):
         return self._add(NodeKind.CONSTANT, const=1 if value else 0)
 
-    def op(self, operation, *parents):
-        return self._add(NodeKind.OPERATION, op=Operation(operation), parents=parents)
+    def op(self, operation, *parents, flags=0):
+        return self._add(NodeKind.OPERATION, op=Operation(operation), parents=parents, flags=flags)
 
     def output_bit(self, field, bit, parent):
         return self._add(NodeKind.OUTPUT, field=field, bit=bit, parents=(parent,))
@@ -103,6 +103,9 @@ class Circuit:
     def not_(self, a): return self.op(Operation.NOT, a)
     def nand(self, a, b): return self.op(Operation.NAND, a, b)
     def xor(self, a, b): return self.op(Operation.XOR, a, b)
+    def xor_fast(self, a, b):
+        """one bootstrap (OpenFHE BINGATE XOR_FAST) instead of the three of EvalBinGate(XOR): HERDB_NODE_FAST"""
+        return self.op(Operation.XOR, a, b, flags=1)
     def mux(self, sel, a, b): return self.op(Operation.MUX, sel, a, b)
 
     def xor_wire(self, a, b):
@@ -129,8 +132,8 @@ class Circuit:
     # -- C ABI -----------------------------------------------------------------------------------
     def to_c(self):
         nodes = (herdb_node * max(1, len(self.nodes)))()
-        for i, (k, op, cv, tp, fd, bt) in enumerate(self.nodes):
-            nodes[i] = herdb_node(k, op, cv, 0, tp, fd, bt)
+        for i, (k, op, cv, tp, fd, bt, fl) in enumerate(self.nodes):
+            nodes[i] = herdb_node(k, op, cv, fl, tp, fd, bt)
         edges = (herdb_edge * max(1, len(self.edges)))()
         for i, (f, t) in enumerate(self.edges):
             edges[i] = herdb_edge(f, t)
@@ -151,7 +154,9 @@ class Circuit:
 # circuit builders for the BASELINE.json configs.  `basis="wire"` uses only AND/OR/NOT (what a herd
 # client can actually send); `basis="model"` uses the XOR / MUX operations of operation.hpp.
 def _xor(c, a, b, basis):
-    return c.xor_wire(a, b) if basis == "wire" else c.xor(a, b)
+    """basis "wire": AND/OR/NOT only (what herdsman's proto can carry); "model": XOR nodes, lowered by the backend
+    to the three-gate form of v1.0.x EvalBinGate(XOR); "fast": XOR nodes flagged HERDB_NODE_FAST, one bootstrap each"""
+    return c.xor_wire(a, b) if basis == "wire" else c.xor_fast(a, b) if basis == "fast" else c.xor(a, b)
 
 
 def _full_adder(c, a, b, cin, basis):

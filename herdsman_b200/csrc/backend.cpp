@@ -402,9 +402,10 @@ extern "C" int herdb_eval_circuit_rows_dev(herdb_ctx* ctx, const char* session, 
     return drain(ctx, d);
 }
 
-// host rows -> devices (contiguous row slices, one host thread per device) -> host rows
-static int eval_rows_host(herdb_ctx* ctx, const char* session, const CompiledCircuit& cc,
-                          const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows) {
+// host rows -> devices (contiguous row slices, one host thread per device) -> host rows.  `stages` is a chain of
+// map circuits: the output row of stage k is the input row of stage k+1 and stays in HBM (two ping-pong buffers).
+static int eval_stages_host(herdb_ctx* ctx, const char* session, const std::vector<const CompiledCircuit*>& stages,
+                            const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows) {
     const size_t G = ctx->devs.size();
     std::vector<int> rcs(G, HERDB_OK);
     auto run_slice = [&](size_t di) {
@@ -418,17 +419,26 @@ static int eval_rows_host(herdb_ctx* ctx, const char* session, const CompiledCir
             if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
             const size_t w = key->n + 1;
             // bound the staging buffers: process the slice in super-chunks of rows
-            const size_t in_row = (size_t)cc.in_bits * w * 2, out_row = (size_t)cc.out_bits * w * 2;
-            const size_t per_row = in_row + out_row + bytes_per_row(cc, key->n);
+            const size_t in_row = (size_t)stages.front()->in_bits * w * 2, out_row = (size_t)stages.back()->out_bits * w * 2;
+            size_t buf_row = std::max(in_row, out_row), scratch_row = 0;
+            for (const CompiledCircuit* cc : stages) {
+                buf_row = std::max(buf_row, std::max((size_t)cc->in_bits, (size_t)cc->out_bits) * w * 2);
+                scratch_row = std::max(scratch_row, bytes_per_row(*cc, key->n));
+            }
+            const size_t per_row = 2 * buf_row + scratch_row;
             const size_t step = std::max<size_t>(1, std::min(rows, ctx->mem_budget / std::max<size_t>(1, per_row)));
-            int rc = grow(ctx, (void**)&d.io_in, &d.io_in_bytes, std::max<size_t>(16, step * in_row)); if (rc) return rc;
-            rc = grow(ctx, (void**)&d.io_out, &d.io_out_bytes, std::max<size_t>(16, step * out_row)); if (rc) return rc;
+            int rc = grow(ctx, (void**)&d.io_in, &d.io_in_bytes, std::max<size_t>(16, step * buf_row)); if (rc) return rc;
+            rc = grow(ctx, (void**)&d.io_out, &d.io_out_bytes, std::max<size_t>(16, step * buf_row)); if (rc) return rc;
             for (size_t s0 = 0; s0 < rows; s0 += step) {
                 const size_t cnt = std::min(step, rows - s0);
-                if (in_row) CU(cudaMemcpyAsync(d.io_in, (const uint8_t*)rows_in + (r0 + s0) * in_row, cnt * in_row, cudaMemcpyHostToDevice, d.stream));
+                u16 *src = d.io_in, *dst = d.io_out;
+                if (in_row) CU(cudaMemcpyAsync(src, (const uint8_t*)rows_in + (r0 + s0) * in_row, cnt * in_row, cudaMemcpyHostToDevice, d.stream));
                 d.stats.h2d_bytes += cnt * in_row;
-                rc = run_circuit_dev(ctx, d, *key, cc, d.io_in, d.io_out, cnt); if (rc) return rc;
-                if (out_row) CU(cudaMemcpyAsync((uint8_t*)rows_out + (r0 + s0) * out_row, d.io_out, cnt * out_row, cudaMemcpyDeviceToHost, d.stream));
+                for (const CompiledCircuit* cc : stages) {
+                    rc = run_circuit_dev(ctx, d, *key, *cc, src, dst, cnt); if (rc) return rc;
+                    std::swap(src, dst);
+                }
+                if (out_row) CU(cudaMemcpyAsync((uint8_t*)rows_out + (r0 + s0) * out_row, src, cnt * out_row, cudaMemcpyDeviceToHost, d.stream));
                 d.stats.d2h_bytes += cnt * out_row;
                 rc = drain(ctx, d); if (rc) return rc;
             }
@@ -444,6 +454,32 @@ static int eval_rows_host(herdb_ctx* ctx, const char* session, const CompiledCir
     }
     for (int rc : rcs) if (rc) return rc;
     return HERDB_OK;
+}
+
+static int eval_rows_host(herdb_ctx* ctx, const char* session, const CompiledCircuit& cc,
+                          const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows) {
+    return eval_stages_host(ctx, session, std::vector<const CompiledCircuit*>{&cc}, rows_in, rows_out, n_rows);
+}
+
+extern "C" int herdb_eval_pipeline_rows(herdb_ctx* ctx, const char* session, const herdb_circuit* const* circuits, size_t n_stages,
+                                        const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows) {
+    if (!ctx || !session || !circuits || !n_stages) return HERDB_ERR_ARG;
+    std::vector<CompiledCircuit> cc(n_stages);
+    std::vector<const CompiledCircuit*> stages;
+    for (size_t k = 0; k < n_stages; ++k) {
+        std::string err;
+        if (!circuits[k]) return HERDB_ERR_ARG;
+        int rc = compile_circuit(circuits[k], cc[k], err);
+        if (rc) { ctx->set_error("circuit of stage " + std::to_string(k) + ": " + err); return rc; }
+        if (k && cc[k].in_bits != cc[k - 1].out_bits) {
+            ctx->set_error("pipeline: stage " + std::to_string(k) + " does not take the row stage " + std::to_string(k - 1) + " produces");
+            return HERDB_ERR_ARG;
+        }
+        stages.push_back(&cc[k]);
+    }
+    if (!n_rows) return HERDB_OK;
+    if ((!rows_in && cc.front().in_bits) || (!rows_out && cc.back().out_bits)) return HERDB_ERR_ARG;
+    return eval_stages_host(ctx, session, stages, rows_in, rows_out, n_rows);
 }
 
 extern "C" int herdb_eval_circuit_rows(herdb_ctx* ctx, const char* session, const herdb_circuit* circuit,

@@ -112,6 +112,7 @@ int compile_circuit(const herdb_circuit* c, CompiledCircuit& out, std::string& e
             case HERDB_OP_NAND: val[id] = add_gate(HERDB_GATE_NAND, a, val[par[1]]); break;
             case HERDB_OP_XOR: {   // OpenFHE v1.0.x EvalBinGate(XOR): OR(AND(a, !b), AND(!a, b))
                 const Value b = val[par[1]];
+                if (nd.flags & HERDB_NODE_FAST) { val[id] = add_gate(HERDB_GATE_XOR_FAST, a, b); break; }   // BINGATE XOR_FAST, one bootstrap
                 Value g1 = add_gate(HERDB_GATE_AND, a, negate(b));
                 Value g2 = add_gate(HERDB_GATE_AND, negate(a), b);
                 val[id] = add_gate(HERDB_GATE_OR, g1, g2);

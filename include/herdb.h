@@ -70,12 +70,18 @@ enum herdb_operation { HERDB_OP_AND = 0, HERDB_OP_OR, HERDB_OP_NOT, HERDB_OP_XOR
 enum herdb_node_kind { HERDB_NODE_INPUT = 0, HERDB_NODE_OUTPUT = 1,
                        HERDB_NODE_CONSTANT = 2, HERDB_NODE_OPERATION = 3 };
 
+/* HERDB_NODE_FAST on an XOR node: evaluate it as ONE bootstrap with OpenFHE's BINGATE XOR_FAST
+ * (2*(ct1 - ct2), gate constant 5q/8) instead of the OR(AND(a,!b), AND(!a,b)) form that v1.0.x
+ * EvalBinGate(XOR) expands to.  Never set by the reference (its wire format cannot even carry XOR,
+ * node.proto:25-30); an opt-in of this backend's own circuit builders. */
+enum herdb_node_flags { HERDB_NODE_FAST = 1 };
+
 /* node_t (nodes.hpp:12-43): which fields are meaningful depends on kind */
 typedef struct herdb_node {
     uint8_t  kind;        /* herdb_node_kind                                        */
     uint8_t  op;          /* herdb_operation            (OPERATION)                 */
     uint8_t  const_val;   /* 0/1                        (CONSTANT)                  */
-    uint8_t  reserved;
+    uint8_t  flags;       /* herdb_node_flags           (OPERATION)                 */
     uint32_t tuple;       /* InputNode::tuple_index     (INPUT)                     */
     uint32_t field;       /* field_index                (INPUT, OUTPUT)             */
     uint32_t bit;         /* bit_index, LSB = 0         (INPUT, OUTPUT)             */
@@ -172,6 +178,12 @@ int herdb_eval_gate_batch(herdb_ctx* ctx, const char* session_uuid, int device, 
                           const uint16_t* ct_a, const uint16_t* ct_b, uint16_t* ct_out, size_t batch);
 int herdb_eval_circuit_rows(herdb_ctx* ctx, const char* session_uuid, const herdb_circuit* circuit,
                             const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows);
+/* A chain of map stages evaluated back to back (execution_service.cpp:524-549 creates one intermediate
+ * frame per stage): the output row of stage k is the input row of stage k+1 and never leaves HBM; only the
+ * first stage's rows go up and the last stage's rows come down. */
+int herdb_eval_pipeline_rows(herdb_ctx* ctx, const char* session_uuid,
+                             const herdb_circuit* const* circuits, size_t n_stages,
+                             const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows);
 /* Device-resident variants (inputs/outputs already in HBM of ctx device `device`;
  * dense layout, ciphertext stride n+1 u16).  Work is enqueued on the backend's
  * stream for that device and the call returns after synchronising it. */

@@ -598,6 +598,7 @@ static void eval_row(const orc_ctx* c, const herdb_circuit* circ, const circ_pla
             case HERDB_OP_NAND: orc_eval_bin_gate(c, HERDB_GATE_NAND, x, y, v); break;
             case HERDB_OP_NOT:  orc_eval_not(c, x, v); break;
             case HERDB_OP_XOR:  /* OpenFHE v1.0.x EvalBinGate(XOR): OR(AND(a, !b), AND(!a, b)) */
+                if (nd->flags & HERDB_NODE_FAST) { orc_eval_bin_gate(c, HERDB_GATE_XOR_FAST, x, y, v); break; }   /* BINGATE XOR_FAST */
                 orc_eval_not(c, x, tmp); orc_eval_not(c, y, tmp + w);
                 orc_eval_bin_gate(c, HERDB_GATE_AND, x, tmp + w, tmp + 2 * w);
                 orc_eval_bin_gate(c, HERDB_GATE_AND, tmp, y, tmp + 3 * w);

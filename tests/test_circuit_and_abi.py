@@ -54,7 +54,7 @@ BUILDERS = [
 ]
 
 
-@pytest.mark.parametrize("basis", ["wire", "model"])
+@pytest.mark.parametrize("basis", ["wire", "model", "fast"])
 @pytest.mark.parametrize("name,build,nin,plain,bits", BUILDERS)
 def test_circuit_builders_plain_semantics(name, build, nin, plain, bits, basis):
     c = build(basis)
@@ -88,6 +88,19 @@ def test_analyze_counts_and_level_structure():
     big = api.analyze(cm.multiply_circuit(32))
     assert big["slots"] < big["boot_gates"] / 4                          # liveness reuse keeps the slot file small
     assert api.analyze(cm.compare_circuit(32))["boot_gates"] == 187
+
+
+def test_fast_xor_nodes_cost_one_bootstrap_and_decrypt(test_key):
+    """HERDB_NODE_FAST (include/herdb.h): an XOR node becomes one XOR_FAST bootstrap; the oracle's interpreter honours
+    the same flag, and the encrypted result still decrypts to the plaintext sum"""
+    wire, fast = api.analyze(cm.adder_circuit(8, "wire")), api.analyze(cm.adder_circuit(8, "fast"))
+    assert wire["boot_gates"] == 64 and fast["boot_gates"] == 34 and fast["levels"] < wire["levels"]
+    c = cm.adder_circuit(8, "fast")
+    x = np.array([200, 13, 255]); y = np.array([100, 29, 255])
+    bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
+    rows = api.client_encrypt_bits(test_key["n"], test_key["sk"], bits, seed=5)
+    out = po.Oracle(test_key["blob"]).circuit_rows(c.to_c(), rows, 8)
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(test_key["n"], test_key["sk"], out)), (x + y) % 256)
 
 
 def test_not_and_constants_cost_no_bootstrap():

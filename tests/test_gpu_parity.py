@@ -91,8 +91,10 @@ def test_std128_large_batch_decrypts(backend, std_session):
 @pytest.mark.parametrize("name,build,bits_in,plain", [
     ("add8", lambda: cm.adder_circuit(8), (8, 8), lambda x, y: (x + y) % 256),
     ("add8_model", lambda: cm.adder_circuit(8, "model"), (8, 8), lambda x, y: (x + y) % 256),
+    ("add8_fast", lambda: cm.adder_circuit(8, "fast"), (8, 8), lambda x, y: (x + y) % 256),      # XOR nodes as one XOR_FAST bootstrap
     ("lt8", lambda: cm.compare_circuit(8), (8, 8), lambda x, y: (x < y).astype(np.uint64)),
     ("mul8", lambda: cm.multiply_circuit(8), (8, 8), lambda x, y: (x * y) % 256),
+    ("mul8_fast", lambda: cm.multiply_circuit(8, "fast"), (8, 8), lambda x, y: (x * y) % 256),
 ])
 def test_circuit_bit_exact_test_params(backend, test_session, name, build, bits_in, plain):
     s = test_session

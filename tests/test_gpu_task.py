@@ -166,3 +166,32 @@ def test_reduce_rows_max(world):
     got = w["wg"].backend.reduce_rows(w["session"], c, rows)
     assert cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got))[0] == vals.max()
     assert np.array_equal(got, _oracle_tree_fold(w["oracle"], c, rows))
+
+
+def test_pipeline_rows_keep_intermediates_on_device(world):
+    """herdb_eval_pipeline_rows: add -> compare -> select with the intermediate rows resident in HBM gives the
+    same ciphertexts as the three stages evaluated one by one (and as the oracle)"""
+    w = world
+    n_rows = 6
+    rng = np.random.default_rng(8)
+    a = rng.integers(0, 256, n_rows); b = rng.integers(0, 256, n_rows); t = rng.integers(0, 256, n_rows)
+    D = cm.DataType
+    s1 = cm.Circuit([[D.UINT8, D.UINT8, D.UINT8]], [("s", D.UINT8), ("t", D.UINT8)])
+    s1.output_word(0, cm._ripple_add(s1, s1.input_word(0, 0), s1.input_word(0, 1), "wire")); s1.output_word(1, s1.input_word(0, 2))
+    s2 = cm.Circuit([[D.UINT8, D.UINT8]], [("lt", D.BIT), ("s", D.UINT8), ("t", D.UINT8)])
+    xs, ys = s2.input_word(0, 0), s2.input_word(0, 1)
+    s2.output_bit(0, 0, cm._less_than(s2, xs, ys, "wire")); s2.output_word(1, xs); s2.output_word(2, ys)
+    s3 = cm.select_circuit(8)
+    bits = np.concatenate([cm.pack_words(a, 8), cm.pack_words(b, 8), cm.pack_words(t, 8)], axis=1)
+    rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=45)
+    be = w["wg"].backend
+    be.load_key(w["session"])
+    got = be.eval_pipeline_rows(w["session"], [s1, s2, s3], rows)
+    ref = rows
+    for c in (s1, s2, s3):
+        ref = w["oracle"].circuit_rows(c.to_c(), ref, c.out_bits)
+    assert np.array_equal(got, ref)
+    s = (a + b) % 256
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got)), np.where(s < t, s, t))
+    with pytest.raises(api.HerdbError):                          # stage 2 does not take stage 1's row
+        be.eval_pipeline_rows(w["session"], [s1, s3], rows)
