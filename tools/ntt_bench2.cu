@@ -18,7 +18,7 @@ struct Smem {
 };
 
 template <int WARPS, int REGCAP>
-__global__ void __launch_bounds__(WARPS * 32, 1) k(const u32* ftw_g, const u32* itw_g, u32* out, int iters) {
+__global__ void __launch_bounds__(WARPS * 32, 1) k(const u32* ftw_g, const u32* itw_g, u32* out, int iters, int skew = 0) {
     extern __shared__ __align__(16) unsigned char raw[];
     Smem& S = *reinterpret_cast<Smem*>(raw);
     const u32 tid = threadIdx.x, lane = tid & 31, warp = (tid >> 5) & 7;
@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k(const u32* ftw_g, const u32* 
     __syncthreads();
     const int c = warp >> 1, j = warp & 1;
     for (int it = 0; it < iters; ++it) {
+        if (skew && (warp & 4)) { const long long t0 = clock64(); while (clock64() - t0 < skew) { } }
         u32 x[32];
         load_contig(S.acc[c][j], lane, x);
         if (!(REGCAP & 2)) {
@@ -110,5 +111,15 @@ int main() {
     run<8, 8>(dftw, ditw, dout, sms); run<8, 9>(dftw, ditw, dout, sms); run<8, 10>(dftw, ditw, dout, sms); run<8, 12>(dftw, ditw, dout, sms);
     run<8, 14>(dftw, ditw, dout, sms); run<8, 15>(dftw, ditw, dout, sms);
     run<12, 8>(dftw, ditw, dout, sms); run<12, 15>(dftw, ditw, dout, sms);
+    // second warp of every scheduler started `skew` clocks late in every iteration (8 warps, full phase A)
+    for (int skew : {0, 200, 500, 1000, 2000, 4000}) {
+        cudaFuncSetAttribute(k<8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+        cudaEventRecord(a);
+        k<8, 0><<<sms, 256, sizeof(Smem)>>>(dftw, ditw, dout, 400, skew);
+        cudaEventRecord(b); cudaEventSynchronize(b);
+        float ms; cudaEventElapsedTime(&ms, a, b);
+        printf("skew %4d clk: %8.3f ms  %7.0f clk per phase A  [%s]\n", skew, ms, ms * 1e-3 * 1.965e9 / 400, cudaGetErrorString(cudaGetLastError()));
+    }
     return 0;
 }
