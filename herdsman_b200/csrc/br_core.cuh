@@ -72,6 +72,7 @@ struct BrSmem {
     u16 lwe[C][kLweMax + 8];
     u32 gate_b[C];               // prepared b and gate code per ciphertext
     u32 gate_code[C];
+    alignas(8) unsigned long long bar;   // mbarrier of the step-start bulk copies (key rows 0, 1 and the monomial rows)
 };
 
 constexpr u32 kAccInitPos = cmulmod(kQ / 8 + 1, kNInv);             // +(Q/8+1) / N
@@ -93,7 +94,9 @@ HERDB_HD u32 operand_word(const Pool* pools, u32 pool, u32 idx, u32 flags, u32 r
 
 // ------------------------------------------------------------------------------------------------
 template <int kC, class Env>
-HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32 group) {
+// `bar_phase0`: parity of the number of bulk-copy phases S.bar has completed before this group (the caller
+// initialises S.bar once, with one expected arrival, and runs groups back to back: steps of earlier groups)
+HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32 group, u32 bar_phase0) {
     constexpr u32 kThreads = 64 * kC;
     static_assert(kC == 4, "the key staging scheme recycles four digit slots for the four (sign, column) pieces");
     const u32 tid = env.tid();
@@ -148,30 +151,40 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 
     // ---- EvalAcc: n CMUX steps (AddToAccCGGI)
     for (u32 i = 0; i < P.steps; ++i) {
-        // Key slice of this step, staged by cp.async.  A thread copies exactly the 16-byte pieces it will
-        // consume (4 (sign, column) pieces per digit), so completion needs cp.async.wait_group only, no
-        // barrier.  Digits 0 and 1 go to the staging ring now and land during phase A; later digits are
-        // issued inside phase B into the ring and into the digit slots this thread has already consumed.
+        // Key slice of this step.  Rows 0 and 1 and the eight monomial rows X^(+-a_i) - 1 (64 KiB, sixteen 4 KiB
+        // pieces) are fetched by TMA bulk copies that ONE thread issues right after the barrier that ended the
+        // previous step (every thread has finished reading the destinations); they land during phase A and are
+        // awaited on an mbarrier at the start of phase B.  Rows 2..7 cannot be fetched that way: their
+        // destinations are slots a thread frees in the middle of the MAC loop, so each thread copies exactly the
+        // 16-byte pieces it will itself consume with cp.async (completion = cp.async.wait_group, no barrier):
+        // into the ring stage and the digit slots it has already read.
         const u32* K = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
         const u32 phys_b = swz(4 * tid);
+        const u32 lin_b = 4 * tid;                                       // staging ring and monomials are stored linearly
         auto stage_key = [&](int r, u32* dst0, u32 dst_stride) {      // piece (s, jo) of digit r -> dst0 + (2*s + jo)*dst_stride
 #pragma unroll
             for (int s = 0; s < 2; ++s)
 #pragma unroll
                 for (int jo = 0; jo < 2; ++jo) env.cp16(dst0 + (2 * s + jo) * dst_stride, K + ((s * kDG2 + r) * 2 + jo) * kN);
         };
-        stage_key(0, &S.kst[0][0][phys_b], kN);
-        // monomial rows X^(+-a_i) - 1 of the four ciphertexts ride in the same group (consumed at the end of phase B)
+        if (tid == 0) {
+            const u32* Kb = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN);
+            env.bulk_begin(&S.bar, (2 * 4 + 2 * kC) * kN * 4);
 #pragma unroll
-        for (int cc = 0; cc < kC; ++cc) {
-            const u32 a = S.lwe[cc][i];
-            const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
-            const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
-            env.cp16(&S.mono[cc][0][phys_b], P.mono + (size_t)row_pos * kN + 4 * tid);
-            env.cp16(&S.mono[cc][1][phys_b], P.mono + (size_t)row_neg * kN + 4 * tid);
+            for (int r = 0; r < 2; ++r)
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int jo = 0; jo < 2; ++jo) env.bulk_copy(&S.kst[r][2 * s + jo][0], Kb + ((s * kDG2 + r) * 2 + jo) * kN, kN * 4, &S.bar);
+#pragma unroll
+            for (int cc = 0; cc < kC; ++cc) {
+                const u32 a = S.lwe[cc][i];
+                const u32 row_pos = (kLweQ - a) & (kLweQ - 1);          // monomial X^(2*row_pos) - 1   (ek1, s = +1)
+                const u32 row_neg = a;                                   // monomial X^(2N - 2*row_pos) - 1 (ek2, s = -1)
+                env.bulk_copy(&S.mono[cc][0][0], P.mono + (size_t)row_pos * kN, kN * 4, &S.bar);
+                env.bulk_copy(&S.mono[cc][1][0], P.mono + (size_t)row_neg * kN, kN * 4, &S.bar);
+            }
         }
-        env.cp_commit();
-        stage_key(1, &S.kst[1][0][phys_b], kN); env.cp_commit();
         // ===== phase A: warp = (ciphertext c, component j)
         {
             const int c = warp >> 1, j = warp & 1;
@@ -227,10 +240,11 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             // where row r's key pieces live: r = 0,2,6 ring 0; r = 1,4 ring 1; r = 3,5,7 the consumed digit slots 0,1,2
 #pragma unroll
             for (int r = 0; r < (int)kDG2; ++r) {
-                if (r == 0 || r == 1 || r == 2 || r == 4) env.cp_wait1();      // groups: {0} {1} | {2,3} | {4,5} | {6,7}
+                if (r == 0) env.mbar_wait(&S.bar, (bar_phase0 + i) & 1);                      // rows 0, 1 and the monomials (bulk copies)
+                if (r == 2 || r == 4) env.cp_wait1();                          // cp.async groups: {2,3} | {4,5} | {6,7}
                 if (r == 6) env.cp_wait0();
-                const u32* kbase = (r == 0 || r == 2 || r == 6) ? &S.kst[0][0][phys_b]
-                                 : (r == 1 || r == 4)           ? &S.kst[1][0][phys_b]
+                const u32* kbase = (r == 0 || r == 2 || r == 6) ? &S.kst[0][0][lin_b]
+                                 : (r == 1 || r == 4)           ? &S.kst[1][0][lin_b]
                                                                 : &S.dig[0][(r - 3) / 2][phys_b];
                 constexpr u32 kDigCt = 2 * kDGT * kN;           // words between the digit blocks of two ciphertexts
                 const u32 kstride = (r == 3 || r == 5 || r == 7) ? kDigCt : kN;
@@ -255,15 +269,15 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 // asm operands make the copies wait for this iteration's shared-memory reads (dep, kv).
                 if (r <= 2) {
                     env.cp_fence(dep ^ kv[1][1].v[0]);
-                    stage_key(2 * r + 2, &S.kst[r & 1][0][phys_b], kN);
+                    stage_key(2 * r + 2, &S.kst[r & 1][0][lin_b], kN);
                     stage_key(2 * r + 3, &S.dig[0][r][phys_b], kDigCt);
                     env.cp_commit();
                 }
             }
 #pragma unroll
             for (int c = 0; c < kC; ++c) {
-                const V4 mp = *reinterpret_cast<const V4*>(&S.mono[c][0][phys_b]);
-                const V4 mn = *reinterpret_cast<const V4*>(&S.mono[c][1][phys_b]);
+                const V4 mp = *reinterpret_cast<const V4*>(&S.mono[c][0][lin_b]);
+                const V4 mn = *reinterpret_cast<const V4*>(&S.mono[c][1][lin_b]);
 #pragma unroll
                 for (int jo = 0; jo < 2; ++jo) {
                     V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys_b]);

@@ -35,6 +35,22 @@ struct DevEnv {
     __device__ __forceinline__ void cp_wait1() const { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
     __device__ __forceinline__ void cp_wait0() const { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
     __device__ __forceinline__ void delay(u32 clocks) const { const long long t0 = clock64(); while (clock64() - t0 < (long long)clocks) { } }
+    // TMA bulk copies (cp.async.bulk, global -> shared) completing on an mbarrier
+    __device__ __forceinline__ void mbar_init(unsigned long long* bar, u32 count) const {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((u32)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __device__ __forceinline__ void bulk_begin(unsigned long long* bar, u32 bytes) const {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((u32)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+    }
+    __device__ __forceinline__ void bulk_copy(void* smem_dst, const void* gsrc, u32 bytes, unsigned long long* bar) const {
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"((u32)__cvta_generic_to_shared(smem_dst)), "l"(gsrc), "r"(bytes), "r"((u32)__cvta_generic_to_shared(bar)) : "memory");
+    }
+    __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 parity) const {
+        asm volatile("{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}"
+                     ::"r"((u32)__cvta_generic_to_shared(bar)), "r"(parity) : "memory");
+    }
     // orders the copies that follow after the shared-memory reads whose results feed `dep`
     __device__ __forceinline__ void cp_fence(u32 dep) const { asm volatile("" ::"r"(dep) : "memory"); }
 };
@@ -46,7 +62,10 @@ __global__ void __launch_bounds__(64 * C, 1) blind_rotate_kernel(const __grid_co
     BrSmem<C>& S = *reinterpret_cast<BrSmem<C>*>(smem_raw);
     DevEnv env;
     const u32 groups = (P.jobs + C - 1) / C;
-    for (u32 g = blockIdx.x; g < groups; g += gridDim.x) blind_rotate_group<C>(env, P, S, g);
+    if (threadIdx.x == 0) env.mbar_init(&S.bar, 1);
+    __syncthreads();
+    u32 done = 0;                                                    // bulk-copy phases completed so far = steps of earlier groups
+    for (u32 g = blockIdx.x; g < groups; g += gridDim.x, done += P.steps) blind_rotate_group<C>(env, P, S, g, done & 1);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -38,6 +38,12 @@ struct HostEnv {
     void cp_wait1() { complete(1); }
     void cp_wait0() { complete(0); }
     void cp_fence(u32) {}
+    // bulk copies: issued by one thread right after a CTA barrier and consumed after the next one, so a plain
+    // copy at issue time is ordered correctly by the pthread barriers (the mbarrier wait itself is GPU-only)
+    void mbar_init(unsigned long long*, u32) {}
+    void bulk_begin(unsigned long long*, u32) {}
+    void bulk_copy(void* dst, const void* src, u32 bytes, unsigned long long*) { memcpy(dst, src, bytes); }
+    void mbar_wait(unsigned long long*, u32) {}
     void delay(u32) {}
 };
 
@@ -45,7 +51,7 @@ template <int C> struct ThreadArg { HostEnv env; const BrParams* P; BrSmem<C>* S
 
 template <int C> static void* thread_main(void* a) {
     ThreadArg<C>* t = (ThreadArg<C>*)a;
-    for (u32 g = 0; g < t->groups; ++g) blind_rotate_group<C>(t->env, *t->P, *t->S, g);
+    for (u32 g = 0; g < t->groups; ++g) blind_rotate_group<C>(t->env, *t->P, *t->S, g, (g * t->P->steps) & 1);
     return nullptr;
 }
 
