@@ -11,8 +11,10 @@
  * This file restates OpenFHE v1.0.x's published GINX/CGGI algorithm
  * (binfhe/lib/{binfhe-base-scheme,lwe-pke,rgsw-acc,rgsw-acc-cggi}.cpp,
  * core math: ChineseRemainderTransformFTT) function by function; it is validated
- * semantically (decrypt == plaintext gate, algebraic identities), not against
- * OpenFHE outputs.
+ * semantically (decrypt == plaintext gate, algebraic identities) and against a
+ * second, structurally different restatement (numpy, schoolbook products, no NTT,
+ * OpenFHE's double-precision rounding: tests/test_oracle_independent.py), not
+ * against OpenFHE outputs.
  */
 #ifndef HERDB_ORACLE_H
 #define HERDB_ORACLE_H
