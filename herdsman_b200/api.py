@@ -16,7 +16,7 @@ import threading
 
 import numpy as np
 
-from .circuit import Circuit, herdb_circuit, herdb_circuit_info
+from .circuit import Circuit, herdb_circuit, herdb_circuit_info, herdb_schedule_info
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libherdb.so")
@@ -31,7 +31,7 @@ EXPORTS = [
     "herdb_load_key", "herdb_load_key_mem", "herdb_load_key_dev", "herdb_unload_key", "herdb_key_lwe_n",
     "herdb_map_async", "herdb_reduce_async", "herdb_reduce_rows", "herdb_wait_idle", "herdb_partition_read", "herdb_partition_write", "herdb_partition_rows",
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_pipeline_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
-    "herdb_circuit_analyze", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
+    "herdb_circuit_analyze", "herdb_circuit_schedule", "herdb_circuit_eval_plain", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_client_key_blob_size", "herdb_client_keygen", "herdb_client_encrypt_bits", "herdb_client_decrypt_bits",
 ]
 
@@ -89,6 +89,8 @@ def lib():
         L.herdb_eval_pipeline_rows.argtypes = [vp, cp, C.POINTER(C.POINTER(herdb_circuit)), sz, vp, vp, sz]
         L.herdb_eval_circuit_rows_dev.argtypes = [vp, cp, ci, C.POINTER(herdb_circuit), vp, vp, sz]
         L.herdb_circuit_analyze.argtypes = [C.POINTER(herdb_circuit), C.POINTER(herdb_circuit_info)]
+        L.herdb_circuit_schedule.argtypes = [C.POINTER(herdb_circuit), u64, u32, C.POINTER(herdb_schedule_info), vp, sz]
+        L.herdb_circuit_eval_plain.argtypes = [C.POINTER(herdb_circuit), u64, u32, vp, vp]
         L.herdb_get_stats.argtypes = [vp, ci, C.POINTER(herdb_stats)]
         L.herdb_get_stream.argtypes = [vp, ci, C.POINTER(vp)]
         L.herdb_reset_stats.argtypes = [vp]
@@ -120,6 +122,31 @@ def analyze(circuit: Circuit):
     if rc:
         raise HerdbError(rc)
     return {k: getattr(info, k) for k, _ in herdb_circuit_info._fields_}
+
+
+def schedule(circuit, rows=0, wave_jobs=0):
+    """herdb_circuit_schedule: level widths and grid rounds of the schedule a launch of `rows` rows gets"""
+    cc = circuit.to_c()
+    info = herdb_schedule_info()
+    cap = max(1, analyze(circuit)["levels"])
+    widths = np.zeros(cap, np.uint32)
+    rc = lib().herdb_circuit_schedule(C.byref(cc), rows, wave_jobs, C.byref(info), _ptr(widths), cap)
+    if rc:
+        raise HerdbError(rc)
+    d = {k: getattr(info, k) for k, _ in herdb_schedule_info._fields_}
+    d["level_widths"] = widths[:info.levels].tolist()
+    return d
+
+
+def eval_plain(circuit, in_bits, rows=0, wave_jobs=0):
+    """herdb_circuit_eval_plain: the compiled levels (scheduled for `rows`) run on one row of plaintext bits"""
+    cc = circuit.to_c()
+    in_bits = np.ascontiguousarray(in_bits, np.uint8)
+    out = np.zeros(max(1, circuit.out_bits), np.uint8)
+    rc = lib().herdb_circuit_eval_plain(C.byref(cc), rows, wave_jobs, _ptr(in_bits), _ptr(out))
+    if rc:
+        raise HerdbError(rc)
+    return out[:circuit.out_bits]
 
 
 # ------------------------------------------------------------------------------------------------ partition files

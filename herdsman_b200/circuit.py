@@ -68,6 +68,11 @@ class herdb_circuit_info(C.Structure):
                 ("levels", C.c_uint32), ("max_level_width", C.c_uint32), ("slots", C.c_uint32)]
 
 
+class herdb_schedule_info(C.Structure):
+    _fields_ = [("levels", C.c_uint32), ("max_level_width", C.c_uint32), ("slots", C.c_uint32), ("policy", C.c_uint32),
+                ("rounds_asap", C.c_uint64), ("rounds", C.c_uint64)]
+
+
 class Circuit:
     """herd::common::Circuit: inputs[tuple][field] -> DataType, output[] -> (name, DataType), circuit_graph."""
 

@@ -65,6 +65,16 @@ const DeviceKey* find_key(Device& d, const char* session) {
     return it == d.keys.end() ? nullptr : &it->second;
 }
 
+// what the level scheduler should plan for: n_rows split evenly over `devices` devices, each launch covering a
+// device's share (row chunking by the memory budget only matters far above the row counts where levels have tails)
+SchedHint sched_hint(const herdb_ctx* ctx, size_t n_rows, size_t devices) {
+    SchedHint h;
+    if (ctx->devs.empty() || !devices) return h;
+    h.rows = (n_rows + devices - 1) / devices;
+    h.wave = (u32)ctx->devs[0]->sm_count * kBrCtsPerCta;
+    return h;
+}
+
 // one circuit level (or a single-gate pseudo level): blind rotation then key switch, `rows` rows
 int run_level(herdb_ctx* ctx, Device& d, const DeviceKey& key, const GateDesc* d_gates, u32 n_gates,
               const Pool pools[4], u32 rows, u32* d_trace = nullptr, u32 steps = UINT32_MAX) {
@@ -389,7 +399,7 @@ extern "C" int herdb_eval_circuit_rows_dev(herdb_ctx* ctx, const char* session, 
                                            const uint16_t* d_rows_in, uint16_t* d_rows_out, size_t n_rows) {
     if (!ctx || !session || !circuit || device < 0 || device >= (int)ctx->devs.size()) return HERDB_ERR_ARG;
     CompiledCircuit cc; std::string err;
-    int rc = compile_circuit(circuit, cc, err);
+    int rc = compile_circuit(circuit, cc, err, sched_hint(ctx, n_rows, 1));
     if (rc) { ctx->set_error("circuit: " + err); return rc; }
     if (!n_rows) return HERDB_OK;
     if ((!d_rows_in && cc.in_bits) || (!d_rows_out && cc.out_bits)) return HERDB_ERR_ARG;
@@ -469,7 +479,7 @@ extern "C" int herdb_eval_pipeline_rows(herdb_ctx* ctx, const char* session, con
     for (size_t k = 0; k < n_stages; ++k) {
         std::string err;
         if (!circuits[k]) return HERDB_ERR_ARG;
-        int rc = compile_circuit(circuits[k], cc[k], err);
+        int rc = compile_circuit(circuits[k], cc[k], err, sched_hint(ctx, n_rows, ctx->devs.size()));
         if (rc) { ctx->set_error("circuit of stage " + std::to_string(k) + ": " + err); return rc; }
         if (k && cc[k].in_bits != cc[k - 1].out_bits) {
             ctx->set_error("pipeline: stage " + std::to_string(k) + " does not take the row stage " + std::to_string(k - 1) + " produces");
@@ -486,7 +496,7 @@ extern "C" int herdb_eval_circuit_rows(herdb_ctx* ctx, const char* session, cons
                                        const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows) {
     if (!ctx || !session || !circuit) return HERDB_ERR_ARG;
     CompiledCircuit cc; std::string err;
-    int rc = compile_circuit(circuit, cc, err);
+    int rc = compile_circuit(circuit, cc, err, sched_hint(ctx, n_rows, ctx->devs.size()));
     if (rc) { ctx->set_error("circuit: " + err); return rc; }
     if (!n_rows) return HERDB_OK;
     if ((!rows_in && cc.in_bits) || (!rows_out && cc.out_bits)) return HERDB_ERR_ARG;
@@ -501,6 +511,30 @@ extern "C" int herdb_circuit_analyze(const herdb_circuit* circuit, herdb_circuit
     info->in_bits = cc.in_bits; info->out_bits = cc.out_bits; info->boot_gates = cc.boot_gates;
     info->levels = (u32)cc.levels.size(); info->max_level_width = cc.max_level_width; info->slots = cc.slots;
     return HERDB_OK;
+}
+
+extern "C" int herdb_circuit_schedule(const herdb_circuit* circuit, uint64_t rows, uint32_t wave_jobs,
+                                      herdb_schedule_info* info, uint32_t* level_widths, size_t cap) {
+    if (!circuit || !info) return HERDB_ERR_ARG;
+    CompiledCircuit cc; std::string err;
+    SchedHint hint; hint.rows = rows; hint.wave = wave_jobs;
+    int rc = compile_circuit(circuit, cc, err, hint);
+    if (rc) return rc;
+    info->levels = (u32)cc.levels.size(); info->max_level_width = cc.max_level_width; info->slots = cc.slots;
+    info->policy = cc.policy; info->rounds_asap = cc.rounds_asap; info->rounds = cc.rounds;
+    if (level_widths) for (size_t l = 0; l < cc.levels.size() && l < cap; ++l) level_widths[l] = (u32)cc.levels[l].size();
+    return HERDB_OK;
+}
+
+extern "C" int herdb_circuit_eval_plain(const herdb_circuit* circuit, uint64_t rows, uint32_t wave_jobs,
+                                        const uint8_t* in_bits, uint8_t* out_bits) {
+    if (!circuit) return HERDB_ERR_ARG;
+    CompiledCircuit cc; std::string err;
+    SchedHint hint; hint.rows = rows; hint.wave = wave_jobs;
+    int rc = compile_circuit(circuit, cc, err, hint);
+    if (rc) return rc;
+    if ((!in_bits && cc.in_bits) || (!out_bits && cc.out_bits)) return HERDB_ERR_ARG;
+    return eval_compiled_plain(cc, in_bits, out_bits) ? HERDB_ERR_ARG : HERDB_OK;
 }
 
 // ================================================================================================ measurement hooks
@@ -737,7 +771,7 @@ extern "C" int herdb_map_async(herdb_ctx* ctx, const char* session, const char* 
     if (!ctx || !session || !in_df || !out_df || !circuit) return HERDB_ERR_ARG;
     MapTaskReq t;
     std::string err;
-    int rc = compile_circuit(circuit, t.circuit, err);      // the circuit is copied (compiled) during the call
+    int rc = compile_circuit(circuit, t.circuit, err, sched_hint(ctx, row_count, ctx->devs.size()));   // the circuit is copied (compiled) during the call
     if (rc) { ctx->set_error("circuit: " + err); return rc; }
     t.session = session; t.in_df = in_df; t.out_df = out_df; t.in_part = in_part; t.out_part = out_part;
     t.row_count = row_count; t.done = done; t.user = user;

@@ -25,6 +25,157 @@ struct BootGate {
     u32 slot = 0;
 };
 
+inline bool gate_operand(const Value& v) { return v.pool == kPoolSlots && !(v.flags & kOpConst); }
+
+// ---- level scheduling ------------------------------------------------------------------------------------
+// Every gate may sit on any level between its as-soon-as-possible and its as-late-as-possible one (critical
+// path length fixed).  A level of g gates costs ceil(rows * g / wave) rounds of the blind-rotation grid, so the
+// last round of a level is usually part empty; gates with slack are moved to fill those rounds.  Several
+// deadline-driven list schedules are built and the cheapest kept; ties keep the as-soon-as-possible levels,
+// so a hint can only lower the cost.  The result is the same ciphertexts: a gate's output does not depend on
+// when it runs.
+uint64_t rounds_of(uint64_t gates, const SchedHint& h) { return (gates * h.rows + h.wave - 1) / h.wave; }
+
+uint64_t schedule_cost(const std::vector<u32>& level, u32 depth, const SchedHint& h) {
+    std::vector<u32> width(depth + 1, 0);
+    for (u32 l : level) width[l]++;
+    uint64_t c = 0;
+    for (u32 L = 1; L <= depth; ++L) c += rounds_of(width[L], h);
+    return c;
+}
+
+// mode 1: every level takes the gates that are due, then fills the rounds those need with the most urgent
+//         ready gates;  mode 2: as 1, and a level on which nothing is due still runs one full round if it can
+//         be filled;  mode 3: every level takes the number of ready gates with the best fill (at least the due ones)
+std::vector<u32> list_schedule(const std::vector<BootGate>& gates, const std::vector<std::vector<u32>>& children,
+                               const std::vector<u32>& alap, u32 depth, const SchedHint& h, int mode) {
+    const u32 ng = (u32)gates.size();
+    std::vector<u32> level(ng, 0), pending(ng, 0);
+    std::vector<std::vector<u32>> bucket(depth + 2);
+    for (u32 i = 0; i < ng; ++i) {
+        pending[i] = (gate_operand(gates[i].a) ? 1u : 0u) + (gate_operand(gates[i].b) ? 1u : 0u);
+        if (!pending[i]) bucket[1].push_back(i);
+    }
+    typedef std::pair<u32, u32> Item;                                   // (deadline, gate)
+    std::priority_queue<Item, std::vector<Item>, std::greater<Item>> ready;
+    std::vector<u32> take;
+    for (u32 L = 1; L <= depth; ++L) {
+        for (u32 g : bucket[L]) ready.push(Item(alap[g], g));
+        take.clear();
+        while (!ready.empty() && ready.top().first <= L) { take.push_back(ready.top().second); ready.pop(); }
+        const uint64_t due = take.size(), avail = due + ready.size();
+        uint64_t want = due;
+        if (mode == 3) {
+            double best = -1.0;
+            for (uint64_t k = std::max<uint64_t>(due, 1); k <= avail; ++k) {
+                const double fill = (double)(k * h.rows) / (double)(rounds_of(k, h) * h.wave);
+                if (fill >= best) { best = fill; want = k; }
+            }
+            if (!due && best < 0.97) want = 0;
+        } else {
+            if (due) want = rounds_of(due, h) * h.wave / h.rows;
+            else if (mode == 2 && avail * h.rows >= h.wave) want = h.wave / h.rows;
+        }
+        while (take.size() < want && !ready.empty()) { take.push_back(ready.top().second); ready.pop(); }
+        for (u32 g : take) {
+            level[g] = L;
+            for (u32 ch : children[g]) if (--pending[ch] == 0) bucket[L + 1].push_back(ch);
+        }
+    }
+    return level;
+}
+
+// Local search on a schedule: move single gates inside their dependency window while that strictly lowers the
+// cost, then try to empty the last round of a level by moving exactly the gates that spill into it to levels
+// with room in their last round.
+void improve_schedule(std::vector<u32>& level, const std::vector<BootGate>& gates, const std::vector<std::vector<u32>>& children,
+                      u32 depth, const SchedHint& h) {
+    const u32 ng = (u32)gates.size();
+    std::vector<u32> width(depth + 2, 0);
+    for (u32 l : level) width[l]++;
+    auto window = [&](u32 g, u32& lo, u32& hi) {
+        lo = 1; hi = depth;
+        if (gate_operand(gates[g].a)) lo = std::max(lo, level[gates[g].a.idx] + 1);
+        if (gate_operand(gates[g].b)) lo = std::max(lo, level[gates[g].b.idx] + 1);
+        for (u32 ch : children[g]) hi = std::min(hi, level[ch] - 1);
+    };
+    auto delta = [&](u32 from, u32 to) -> long long {
+        return (long long)rounds_of(width[from] - 1, h) - (long long)rounds_of(width[from], h) +
+               (long long)rounds_of(width[to] + 1, h) - (long long)rounds_of(width[to], h);
+    };
+    for (int pass = 0; pass < 64; ++pass) {
+        bool moved = false;
+        for (u32 g = 0; g < ng; ++g) {                                  // single moves
+            u32 lo, hi; window(g, lo, hi);
+            const u32 A = level[g];
+            u32 bestB = A; long long bestD = 0;
+            for (u32 B = lo; B <= hi; ++B) {
+                if (B == A) continue;
+                const long long d = delta(A, B);
+                if (d < bestD) { bestD = d; bestB = B; }
+            }
+            if (bestB != A) { width[A]--; width[bestB]++; level[g] = bestB; moved = true; }
+        }
+        std::vector<std::vector<u32>> members(depth + 1);
+        for (u32 g = 0; g < ng; ++g) members[level[g]].push_back(g);
+        for (u32 A = 1; A <= depth; ++A) {                              // shed the spill of level A
+            if (!width[A]) continue;
+            const uint64_t keep = (rounds_of(width[A], h) - 1) * h.wave / h.rows;
+            const u32 need = width[A] - (u32)std::min<uint64_t>(keep, width[A]);
+            if (!need || need > 64) continue;
+            std::vector<std::pair<u32, u32>> done;                      // (gate, old level)
+            for (u32 g : members[A]) {
+                if (level[g] != A) continue;
+                u32 lo, hi; window(g, lo, hi);
+                for (u32 B = lo; B <= hi; ++B) {
+                    if (B == A || !width[B]) continue;
+                    if (rounds_of(width[B] + 1, h) != rounds_of(width[B], h)) continue;
+                    done.push_back(std::make_pair(g, A));
+                    width[A]--; width[B]++; level[g] = B;
+                    break;
+                }
+                if (done.size() == need) break;
+            }
+            if (done.size() == need) moved = true;
+            else for (auto& m : done) { width[level[m.first]]--; width[m.second]++; level[m.first] = m.second; }
+        }
+        if (!moved) break;
+    }
+}
+
+// gates[].level: as-soon-as-possible on entry, the chosen schedule on return (levels renumbered without gaps)
+void schedule_levels(std::vector<BootGate>& gates, const std::vector<Value>& out_val, const SchedHint& h, CompiledCircuit& out) {
+    const u32 ng = (u32)gates.size();
+    if (!h.rows || !h.wave || !ng) return;
+    u32 depth = 0;
+    for (auto& g : gates) depth = std::max(depth, g.level);
+    std::vector<std::vector<u32>> children(ng);
+    for (u32 i = 0; i < ng; ++i) {
+        if (gate_operand(gates[i].a)) children[gates[i].a.idx].push_back(i);
+        if (gate_operand(gates[i].b)) children[gates[i].b.idx].push_back(i);
+    }
+    (void)out_val;
+    std::vector<u32> asap(ng), alap(ng, depth);
+    for (u32 i = 0; i < ng; ++i) asap[i] = gates[i].level;
+    for (u32 i = ng; i-- > 0;)                                           // gates are in topological order
+        for (u32 ch : children[i]) alap[i] = std::min(alap[i], alap[ch] - 1);
+    std::vector<u32> best = asap;
+    out.rounds_asap = out.rounds = schedule_cost(asap, depth, h);
+    auto offer = [&](std::vector<u32> cand, u32 policy) {
+        improve_schedule(cand, gates, children, depth, h);
+        const uint64_t c = schedule_cost(cand, depth, h);
+        if (c < out.rounds) { out.rounds = c; best = cand; out.policy = policy; }
+    };
+    for (int mode = 1; mode <= 3; ++mode) offer(list_schedule(gates, children, alap, depth, h, mode), (u32)mode);
+    offer(alap, 4);
+    offer(asap, 5);
+    std::vector<u32> used(depth + 2, 0), renum(depth + 2, 0);
+    for (u32 l : best) used[l] = 1;
+    u32 next = 0;
+    for (u32 L = 1; L <= depth; ++L) if (used[L]) renum[L] = ++next;
+    for (u32 i = 0; i < ng; ++i) gates[i].level = renum[best[i]];
+}
+
 Value negate(Value v) {
     if (v.flags & kOpConst) v.flags ^= kOpConstVal; else v.flags ^= kOpNeg;
     return v;
@@ -32,7 +183,7 @@ Value negate(Value v) {
 
 }  // namespace
 
-int compile_circuit(const herdb_circuit* c, CompiledCircuit& out, std::string& err) {
+int compile_circuit(const herdb_circuit* c, CompiledCircuit& out, std::string& err, SchedHint hint) {
     out = CompiledCircuit();
     if (!c || (!c->nodes && c->n_nodes) || (!c->edges && c->n_edges) || !c->in_tuple_offsets) { err = "null circuit"; return HERDB_ERR_ARG; }
     const u32 nn = (u32)c->n_nodes;
@@ -130,13 +281,15 @@ int compile_circuit(const herdb_circuit* c, CompiledCircuit& out, std::string& e
     for (u32 o = 0; o < out.out_bits; ++o)
         if (!out_set[o]) { err = "output bit without an output node"; return HERDB_ERR_ARG; }
 
+    schedule_levels(gates, out_val, hint, out);
+
     // liveness: last level reading each gate result
     for (auto& g : gates) {
-        if (g.a.pool == kPoolSlots && !(g.a.flags & kOpConst)) gates[g.a.idx].last_use = std::max(gates[g.a.idx].last_use, g.level);
-        if (g.b.pool == kPoolSlots && !(g.b.flags & kOpConst)) gates[g.b.idx].last_use = std::max(gates[g.b.idx].last_use, g.level);
+        if (gate_operand(g.a)) gates[g.a.idx].last_use = std::max(gates[g.a.idx].last_use, g.level);
+        if (gate_operand(g.b)) gates[g.b.idx].last_use = std::max(gates[g.b.idx].last_use, g.level);
     }
     for (auto& v : out_val)
-        if (v.pool == kPoolSlots && !(v.flags & kOpConst)) gates[v.idx].last_use = UINT32_MAX;
+        if (gate_operand(v)) gates[v.idx].last_use = UINT32_MAX;
 
     u32 n_levels = 0;
     for (auto& g : gates) n_levels = std::max(n_levels, g.level);
@@ -186,6 +339,44 @@ int compile_circuit(const herdb_circuit* c, CompiledCircuit& out, std::string& e
         out.outs[o] = d;
     }
     return HERDB_OK;
+}
+
+int eval_compiled_plain(const CompiledCircuit& cc, const uint8_t* in_bits, uint8_t* out_bits) {
+    std::vector<uint8_t> slots(cc.slots, 0), fresh;
+    std::vector<u32> read_at(cc.slots, 0), written_at(cc.slots, 0);       // level (1-based) of the last read / write
+    auto operand = [&](uint8_t pool, u32 idx, uint8_t flags) -> uint8_t {
+        if (flags & kOpConst) return (flags & kOpConstVal) ? 1 : 0;
+        const uint8_t v = pool == kPoolSlots ? slots[idx] : in_bits[idx];
+        return (flags & kOpNeg) ? (uint8_t)(v ^ 1) : v;
+    };
+    u32 lev = 0;
+    for (auto& L : cc.levels) {
+        ++lev;
+        fresh.clear();
+        for (auto& g : L) {                                  // a level reads the slot file as the previous level left it
+            if (!(g.flag_a & kOpConst) && g.pool_a == kPoolSlots) read_at[g.idx_a] = lev;
+            if (!(g.flag_b & kOpConst) && g.pool_b == kPoolSlots) read_at[g.idx_b] = lev;
+            const uint8_t a = operand(g.pool_a, g.idx_a, g.flag_a), b = operand(g.pool_b, g.idx_b, g.flag_b);
+            uint8_t r = 0;
+            switch (g.gate) {
+            case HERDB_GATE_OR: r = a | b; break;
+            case HERDB_GATE_AND: r = a & b; break;
+            case HERDB_GATE_NOR: r = (a | b) ^ 1; break;
+            case HERDB_GATE_NAND: r = (a & b) ^ 1; break;
+            case HERDB_GATE_XOR_FAST: r = a ^ b; break;
+            case HERDB_GATE_XNOR_FAST: r = a ^ b ^ 1; break;
+            }
+            fresh.push_back(r);
+        }
+        for (size_t k = 0; k < L.size(); ++k) {              // gates of a level run concurrently on the device:
+            const u32 o = L[k].idx_out;                      // none may write a slot the level reads or writes
+            if (read_at[o] == lev || written_at[o] == lev) return -1;
+            written_at[o] = lev;
+            slots[o] = fresh[k];
+        }
+    }
+    for (u32 o = 0; o < cc.out_bits; ++o) out_bits[o] = operand(cc.outs[o].pool, cc.outs[o].idx, cc.outs[o].flags);
+    return 0;
 }
 
 }  // namespace herdb

@@ -204,6 +204,23 @@ typedef struct herdb_circuit_info {
 } herdb_circuit_info;
 int herdb_circuit_analyze(const herdb_circuit* circuit, herdb_circuit_info* info);
 
+/* The level schedule a launch of `rows` rows gets on a grid that retires `wave_jobs` jobs (gates x rows) per
+ * round of its persistent CTAs (SM count x 4; the eval entry points pass their own).  The reference evaluates
+ * a row node by node (executor.cpp:98-146); here gates are grouped into dependency levels, and gates with
+ * slack are placed on the level whose last, part-empty round they fill.  rows == 0: as-soon-as-possible
+ * levels.  level_widths (may be NULL) receives min(levels, cap) gate counts. */
+typedef struct herdb_schedule_info {
+    uint32_t levels, max_level_width, slots;
+    uint32_t policy;                /* 0 = as soon as possible kept, else the list schedule that won  */
+    uint64_t rounds_asap, rounds;   /* grid rounds per launch before / after (0 without a hint)       */
+} herdb_schedule_info;
+int herdb_circuit_schedule(const herdb_circuit* circuit, uint64_t rows, uint32_t wave_jobs,
+                           herdb_schedule_info* info, uint32_t* level_widths, size_t cap);
+/* the compiled levels run on plaintext bits (in_bits / out_bits: one byte per bit of a row): a host-side check
+ * of the compiler and its slot reuse.  HERDB_ERR_ARG if two gates of a level conflict on a slot. */
+int herdb_circuit_eval_plain(const herdb_circuit* circuit, uint64_t rows, uint32_t wave_jobs,
+                             const uint8_t* in_bits, uint8_t* out_bits);
+
 /* ------------------------------------------------------------------ measurement hooks */
 typedef struct herdb_stats {
     uint64_t kernel_launches;       /* our kernels launched since create / last reset          */

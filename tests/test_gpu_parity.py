@@ -143,3 +143,29 @@ def test_add8_std128_rows(backend, std_session):
     assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out)), (x + y) % 256)
     ref = s["oracle"].circuit_rows(c.to_c(), rows_in[:4], c.out_bits)      # oracle: ~7 s per row per core
     assert np.array_equal(out[:4], ref)
+
+
+@pytest.mark.parametrize("name,build,plain", [
+    ("add8", lambda: cm.adder_circuit(8), lambda x, y: (x + y) % 256),
+    ("mul8", lambda: cm.multiply_circuit(8), lambda x, y: (x * y) % 256),
+])
+def test_rescheduled_levels_bit_exact(backend, test_session, name, build, plain):
+    """148 rows: the level scheduler (circuit.cpp) moves gates with slack off their as-soon-as-possible level
+    to fill grid rounds; every gate is deterministic, so the ciphertexts must not change"""
+    import torch
+    s = test_session
+    c = build()
+    rows = 148
+    wave = torch.cuda.get_device_properties(0).multi_processor_count * 4
+    sched = api.schedule(c, rows, wave)
+    assert sched["policy"] != 0 and sched["rounds"] < sched["rounds_asap"]       # this test is about a moved schedule
+    rng = np.random.default_rng(8)
+    x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
+    bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
+    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=77)
+    out = backend.eval_circuit_rows(s["name"], c, rows_in)
+    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out)), plain(x, y))
+    ref = s["oracle"].circuit_rows(c.to_c(), rows_in[:6], c.out_bits)
+    assert np.array_equal(out[:6], ref)
+    small = backend.eval_circuit_rows(s["name"], c, rows_in[:5])                  # 5 rows: as-soon-as-possible levels
+    assert np.array_equal(small, out[:5])

@@ -39,13 +39,21 @@ def run_circuit(be, sk, name, circ, cols, bits, plain, seed, oracle_rows, orc):
     info = api.analyze(circ)
     rows = rows_in.shape[0]
     be.eval_circuit_rows("s", circ, rows_in[:min(rows, 64)])                      # warm-up (allocations)
-    be.reset_stats()
-    t0 = time.perf_counter()
-    out = be.eval_circuit_rows("s", circ, rows_in)
-    dt = time.perf_counter() - t0
-    st = be.stats()
+    dt, spent = None, 0.0
+    while dt is None or (spent < 3.0 and dt < 1.5):          # short configurations: best of a few runs
+        be.reset_stats()
+        t0 = time.perf_counter()
+        out = be.eval_circuit_rows("s", circ, rows_in)
+        d = time.perf_counter() - t0
+        spent += d
+        if dt is None or d < dt:
+            dt, st = d, be.stats()
     dec = cm.unpack_words(api.client_decrypt_bits(N, sk, out)).reshape(rows)
     ok = bool(np.array_equal(dec, plain))
+    sm = be.device_sm_count() if hasattr(be, "device_sm_count") else 148
+    sched = api.schedule(circ, rows, sm * 4)
+    info = dict(info, levels=sched["levels"], slots=sched["slots"], max_level_width=sched["max_level_width"],
+                grid_rounds_asap=sched["rounds_asap"], grid_rounds=sched["rounds"])
     line = {"config": name, "rows": rows, "circuit": info, "seconds": dt, "rows_per_s": rows / dt,
             "gates_per_s": rows * info["boot_gates"] / dt, "decrypt_matches_plaintext": ok,
             "kernel_ms": {"blind_rotate": st["blind_rotate_ms"], "keyswitch": st["keyswitch_ms"]},
