@@ -77,6 +77,99 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k(const u32* ftw_g, const u32* 
         for (u32 w = tid; w < 4 * 2 * kDGT * kN; w += 256) out[w] = canon32((&S.dig[0][0][0])[w]);
 }
 
+// Helper-warp variant: 8 transform warps (inverse NTT, decomposition, forward NTTs of digits 0 and 1) plus 4
+// helper warps, one per scheduler, that take the forward NTT of digit 2 of the two polynomials of their scheduler
+// (digits handed over as packed bytes in shared memory, named barriers).  12 warps, 3 per scheduler.
+struct Smem2 : Smem { u32 d2[8][kN / 4]; };
+__global__ void __launch_bounds__(384, 1) k_helper(const u32* ftw_g, const u32* itw_g, u32* out, int iters) {
+    extern __shared__ __align__(16) unsigned char raw[];
+    Smem2& S = *reinterpret_cast<Smem2*>(raw);
+    const u32 tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (u32 w = tid; w < kLaneTwWords; w += 384) { S.itw[w] = itw_g[w]; S.ftw[w] = ftw_g[w]; }
+    for (u32 w = tid; w < 8 * kN; w += 384) (&S.acc[0][0][0])[w] = (w * 2654435761u + blockIdx.x * 97u) % kQ;
+    __syncthreads();
+    for (int it = 0; it < iters; ++it) {
+        if (warp < 8) {
+            const int c = warp >> 1, j = warp & 1;
+            u32 x[32];
+            load_contig(S.acc[c][j], lane, x);
+            inv_pass1(x, S.itw, lane);
+            store_contig(S.dig[c][j], lane, x);
+            __syncwarp();
+            load_strided(S.dig[c][j], lane, x);
+            inv_pass2(x);
+            constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
+            u32 y[2][32];
+#pragma unroll
+            for (int m = 0; m < 8; ++m) {
+                u32 pk = 0;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int kk = 4 * m + q;
+                    u32 t = csub(x[kk], kQ);
+                    const u32 d = (t < (kQ >> 1)) ? t + kB : t + (kB - kQ);
+                    y[0][kk] = d & 127u; y[1][kk] = (d >> 7) & 127u;
+                    pk |= ((d >> 14) & 127u) << (8 * q);
+                }
+                S.d2[warp][m * 32 + lane] = pk;
+            }
+            asm volatile("bar.arrive %0, 64;" ::"r"(1 + (int)warp) : "memory");
+            fwd_pass1_digits_multi<2>(y);
+            store_strided(S.dig[c][j], lane, y[0]); store_strided(S.dig[c][j + 2], lane, y[1]);
+            __syncwarp();
+            load_contig(S.dig[c][j], lane, y[0]); load_contig(S.dig[c][j + 2], lane, y[1]);
+            fwd_pass2_stream_multi<2>(y, S.ftw, lane);
+            store_contig(S.dig[c][j], lane, y[0]); store_contig(S.dig[c][j + 2], lane, y[1]);
+        } else {
+            const int q = warp - 8;
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                const int pw = q + 4 * half, c = pw >> 1, j = pw & 1;
+                asm volatile("bar.sync %0, 64;" ::"r"(1 + pw) : "memory");
+                u32 y[1][32];
+#pragma unroll
+                for (int m = 0; m < 8; ++m) {
+                    const u32 pk = S.d2[pw][m * 32 + lane];
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) y[0][4 * m + b] = (pk >> (8 * b)) & 127u;
+                }
+                fwd_pass1_digits_multi<1>(y);
+                store_strided(S.dig[c][j + 4], lane, y[0]);
+                __syncwarp();
+                load_contig(S.dig[c][j + 4], lane, y[0]);
+                fwd_pass2_stream_multi<1>(y, S.ftw, lane);
+                store_contig(S.dig[c][j + 4], lane, y[0]);
+            }
+        }
+        __syncthreads();
+        if (it + 1 < iters && warp < 8) {
+            const int c = warp >> 1, j = warp & 1;
+            u32 z[32];
+            load_contig(S.dig[c][j + 2], lane, z);
+#pragma unroll
+            for (int kk = 0; kk < 32; ++kk) z[kk] = canon32(z[kk]);
+            store_contig(S.acc[c][j], lane, z);
+        }
+        __syncthreads();
+    }
+    if (blockIdx.x == 0 && tid < 256)
+        for (u32 w = tid; w < 4 * 2 * kDGT * kN; w += 256) out[w] = canon32((&S.dig[0][0][0])[w]);
+}
+void run_helper(const u32* dftw, const u32* ditw, u32* dout, int sms) {
+    cudaFuncSetAttribute(k_helper, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem2));
+    const int iters = 400;
+    k_helper<<<sms, 384, sizeof(Smem2)>>>(dftw, ditw, dout, 4); cudaDeviceSynchronize();
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a);
+    k_helper<<<sms, 384, sizeof(Smem2)>>>(dftw, ditw, dout, iters);
+    cudaEventRecord(b); cudaEventSynchronize(b);
+    float ms; cudaEventElapsedTime(&ms, a, b);
+    cudaFuncAttributes fa; cudaFuncGetAttributes(&fa, k_helper);
+    const double clk = ms * 1e-3 * 1.965e9 / iters, pipe = 2 * 4 * 160 * 8;
+    printf("helper-warp variant, 12 warps/SM (%d regs, %zu B local): %8.3f ms  %7.0f clk per phase A, butterfly pipe need %6.0f -> %.1f %%  [%s]\n",
+           fa.numRegs, (size_t)fa.localSizeBytes, ms, clk, pipe, 100.0 * pipe / clk, cudaGetErrorString(cudaGetLastError()));
+}
+
 template <int WARPS, int REGCAP>
 void run(const u32* dftw, const u32* ditw, u32* dout, int sms) {
     cudaFuncSetAttribute(k<WARPS, REGCAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
@@ -111,6 +204,7 @@ int main() {
     run<8, 8>(dftw, ditw, dout, sms); run<8, 9>(dftw, ditw, dout, sms); run<8, 10>(dftw, ditw, dout, sms); run<8, 12>(dftw, ditw, dout, sms);
     run<8, 14>(dftw, ditw, dout, sms); run<8, 15>(dftw, ditw, dout, sms);
     run<12, 8>(dftw, ditw, dout, sms); run<12, 15>(dftw, ditw, dout, sms);
+    run_helper(dftw, ditw, dout, sms);
     // second warp of every scheduler started `skew` clocks late in every iteration (8 warps, full phase A)
     for (int skew : {0, 200, 500, 1000, 2000, 4000}) {
         cudaFuncSetAttribute(k<8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
