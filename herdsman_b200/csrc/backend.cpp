@@ -227,6 +227,9 @@ extern "C" int herdb_create(herdb_ctx** out, const int* device_ids, int n_device
         if (cudaSetDevice(id) != cudaSuccess) return fail(HERDB_ERR_CUDA);
         cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, id);
         if (cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(HERDB_ERR_CUDA);
+        if (cudaStreamCreateWithFlags(&d->copy, cudaStreamNonBlocking) != cudaSuccess) return fail(HERDB_ERR_CUDA);
+        for (auto& e : d->ev_piece)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return fail(HERDB_ERR_CUDA);
         if (cudaMalloc((void**)&d->mono, mono.size() * 4) != cudaSuccess || cudaMalloc((void**)&d->ftw2, kLaneTwWords * 4) != cudaSuccess ||
             cudaMalloc((void**)&d->itw1, kLaneTwWords * 4) != cudaSuccess) return fail(HERDB_ERR_NOMEM);
         cudaMemcpy(d->mono, mono.data(), mono.size() * 4, cudaMemcpyHostToDevice);
@@ -255,6 +258,8 @@ extern "C" void herdb_destroy(herdb_ctx* ctx) {
         cudaFree(d->mono); cudaFree(d->ftw2); cudaFree(d->itw1); cudaFree(d->slots); cudaFree(d->ext);
         cudaFree(d->gates); cudaFree(d->outs); cudaFree(d->io_in); cudaFree(d->io_out);
         if (d->stream) cudaStreamDestroy(d->stream);
+        if (d->copy) cudaStreamDestroy(d->copy);
+        for (auto& e : d->ev_piece) if (e) cudaEventDestroy(e);
         delete d;
     }
     delete ctx;
@@ -338,6 +343,31 @@ extern "C" int herdb_key_lwe_n(herdb_ctx* ctx, const char* session, uint32_t* n_
 }
 
 // ================================================================================================ file-less entry points
+// single-gate batches over device buffers: descriptor upload + scratch once, then launches over row ranges
+static int gate_batch_prepare(herdb_ctx* ctx, Device& d, int gate, size_t batch, size_t* chunk_out) {
+    int rc = grow(ctx, (void**)&d.gates, &d.gates_cap, sizeof(GateDesc)); if (rc) return rc;
+    GateDesc g{}; g.gate = (uint8_t)gate; g.pool_a = 0; g.pool_b = 2; g.pool_out = 3;
+    CU(cudaMemcpyAsync(d.gates, &g, sizeof g, cudaMemcpyHostToDevice, d.stream));
+    CU(cudaStreamSynchronize(d.stream));      // `g` lives on this stack frame
+    const size_t per_job = (size_t)kExtStride * 2;
+    const size_t chunk = std::min<size_t>(batch, std::max<size_t>(1, std::min<size_t>(ctx->mem_budget / per_job, 0x7FFFFFFF)));
+    *chunk_out = chunk;
+    return grow(ctx, (void**)&d.ext, &d.ext_bytes, chunk * per_job);
+}
+static int gate_batch_launch(herdb_ctx* ctx, Device& d, const DeviceKey& key, const u16* d_a, const u16* d_b, u16* d_out,
+                             size_t first, size_t count, size_t chunk) {
+    const size_t w = key.n + 1;
+    for (size_t r0 = first; r0 < first + count; r0 += chunk) {
+        const u32 rows = (u32)std::min(chunk, first + count - r0);
+        Pool pools[4] = {};
+        pools[0] = Pool{const_cast<u16*>(d_a) + r0 * w, 1, 0};
+        pools[2] = Pool{const_cast<u16*>(d_b) + r0 * w, 1, 0};
+        pools[3] = Pool{d_out + r0 * w, 1, 0};
+        int rc = run_level(ctx, d, key, d.gates, 1, pools, rows); if (rc) return rc;
+    }
+    return HERDB_OK;
+}
+
 extern "C" int herdb_eval_gate_batch_dev(herdb_ctx* ctx, const char* session, int device, int gate,
                                          const uint16_t* d_a, const uint16_t* d_b, uint16_t* d_out, size_t batch) {
     if (!ctx || !session || device < 0 || device >= (int)ctx->devs.size() || gate < 0 || gate > HERDB_GATE_XNOR_FAST) return HERDB_ERR_ARG;
@@ -348,51 +378,66 @@ extern "C" int herdb_eval_gate_batch_dev(herdb_ctx* ctx, const char* session, in
     CU(cudaSetDevice(d.id));
     const DeviceKey* key = find_key(d, session);
     if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
-    int rc = grow(ctx, (void**)&d.gates, &d.gates_cap, sizeof(GateDesc)); if (rc) return rc;
-    GateDesc g{}; g.gate = (uint8_t)gate; g.pool_a = 0; g.pool_b = 2; g.pool_out = 3;
-    CU(cudaMemcpyAsync(d.gates, &g, sizeof g, cudaMemcpyHostToDevice, d.stream));
-    CU(cudaStreamSynchronize(d.stream));
-    const size_t per_job = (size_t)kExtStride * 2;
-    const size_t chunk = std::min<size_t>(batch, std::max<size_t>(1, std::min<size_t>(ctx->mem_budget / per_job, 0x7FFFFFFF)));
-    rc = grow(ctx, (void**)&d.ext, &d.ext_bytes, chunk * per_job); if (rc) return rc;
-    const size_t w = key->n + 1;
-    for (size_t r0 = 0; r0 < batch; r0 += chunk) {
-        const u32 rows = (u32)std::min(chunk, batch - r0);
-        Pool pools[4] = {};
-        pools[0] = Pool{const_cast<u16*>(d_a) + r0 * w, 1, 0};
-        pools[2] = Pool{const_cast<u16*>(d_b) + r0 * w, 1, 0};
-        pools[3] = Pool{d_out + r0 * w, 1, 0};
-        rc = run_level(ctx, d, *key, d.gates, 1, pools, rows); if (rc) return rc;
-    }
+    size_t chunk = 0;
+    int rc = gate_batch_prepare(ctx, d, gate, batch, &chunk); if (rc) return rc;
+    rc = gate_batch_launch(ctx, d, *key, d_a, d_b, d_out, 0, batch, chunk); if (rc) return rc;
     return drain(ctx, d);
 }
 
+// Host buffers.  A large batch is cut into a head of one grid round, a middle and a tail of one round (+ the
+// remainder): the middle's upload rides the copy stream under the head's kernels and the middle's download
+// under the tail's, so only one round's worth of PCIe traffic is exposed.  Pieces are multiples of the round
+// size (SM count x ciphertexts per CTA), so the cut adds no part-empty round.
 extern "C" int herdb_eval_gate_batch(herdb_ctx* ctx, const char* session, int device, int gate,
                                      const uint16_t* a, const uint16_t* b, uint16_t* out, size_t batch) {
-    if (!ctx || !session || device < 0 || device >= (int)ctx->devs.size()) return HERDB_ERR_ARG;
+    if (!ctx || !session || device < 0 || device >= (int)ctx->devs.size() || gate < 0 || gate > HERDB_GATE_XNOR_FAST) return HERDB_ERR_ARG;
     if (!batch) return HERDB_OK;
     if (!a || !b || !out) return HERDB_ERR_ARG;
     Device& d = *ctx->devs[device];
-    size_t bytes;
-    {
-        std::lock_guard<std::mutex> l(d.mu);
-        CU(cudaSetDevice(d.id));
-        const DeviceKey* key = find_key(d, session);
-        if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
-        bytes = batch * (key->n + 1) * 2;
-        int rc = grow(ctx, (void**)&d.io_in, &d.io_in_bytes, 2 * bytes); if (rc) return rc;
-        rc = grow(ctx, (void**)&d.io_out, &d.io_out_bytes, bytes); if (rc) return rc;
-        CU(cudaMemcpyAsync(d.io_in, a, bytes, cudaMemcpyHostToDevice, d.stream));
-        CU(cudaMemcpyAsync((uint8_t*)d.io_in + bytes, b, bytes, cudaMemcpyHostToDevice, d.stream));
-        d.stats.h2d_bytes += 2 * bytes;
-    }
-    int rc = herdb_eval_gate_batch_dev(ctx, session, device, gate, d.io_in, (u16*)((uint8_t*)d.io_in + bytes), d.io_out, batch);
-    if (rc) return rc;
     std::lock_guard<std::mutex> l(d.mu);
-    CU(cudaMemcpyAsync(out, d.io_out, bytes, cudaMemcpyDeviceToHost, d.stream));
-    CU(cudaStreamSynchronize(d.stream));
-    d.stats.d2h_bytes += bytes;
-    return HERDB_OK;
+    CU(cudaSetDevice(d.id));
+    const DeviceKey* key = find_key(d, session);
+    if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
+    const size_t w = key->n + 1, bytes = batch * w * 2;
+    int rc = grow(ctx, (void**)&d.io_in, &d.io_in_bytes, 2 * bytes); if (rc) return rc;
+    rc = grow(ctx, (void**)&d.io_out, &d.io_out_bytes, bytes); if (rc) return rc;
+    size_t chunk = 0;
+    rc = gate_batch_prepare(ctx, d, gate, batch, &chunk); if (rc) return rc;
+    u16 *da = d.io_in, *db = d.io_in + batch * w, *dout = d.io_out;
+    const size_t wave = (size_t)d.sm_count * kBrCtsPerCta;
+    size_t cut[4] = {0, batch, batch, batch};                      // piece p = [cut[p], cut[p+1])
+    if (batch >= 4 * wave) { cut[1] = wave; cut[2] = batch - wave - batch % wave; }
+    auto h2d = [&](int p, cudaStream_t st) -> cudaError_t {
+        const size_t off = cut[p] * w, cnt = (cut[p + 1] - cut[p]) * w * 2;
+        if (!cnt) return cudaSuccess;
+        cudaError_t e = cudaMemcpyAsync(da + off, a + off, cnt, cudaMemcpyHostToDevice, st);
+        return e != cudaSuccess ? e : cudaMemcpyAsync(db + off, b + off, cnt, cudaMemcpyHostToDevice, st);
+    };
+    auto d2h = [&](int p, cudaStream_t st) -> cudaError_t {
+        const size_t off = cut[p] * w, cnt = (cut[p + 1] - cut[p]) * w * 2;
+        return cnt ? cudaMemcpyAsync(out + off, dout + off, cnt, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+    };
+    CU(h2d(0, d.stream));
+    rc = gate_batch_launch(ctx, d, *key, da, db, dout, cut[0], cut[1] - cut[0], chunk); if (rc) return rc;
+    if (cut[1] < batch) {
+        CU(cudaEventRecord(d.ev_piece[0], d.stream));               // head computed
+        CU(h2d(1, d.copy)); CU(h2d(2, d.copy));
+        CU(cudaEventRecord(d.ev_piece[1], d.copy));                 // middle and tail uploaded
+        CU(cudaStreamWaitEvent(d.stream, d.ev_piece[1], 0));
+        rc = gate_batch_launch(ctx, d, *key, da, db, dout, cut[1], cut[2] - cut[1], chunk); if (rc) return rc;
+        CU(cudaEventRecord(d.ev_piece[2], d.stream));               // middle computed
+        rc = gate_batch_launch(ctx, d, *key, da, db, dout, cut[2], cut[3] - cut[2], chunk); if (rc) return rc;
+        CU(cudaStreamWaitEvent(d.copy, d.ev_piece[0], 0));
+        CU(d2h(0, d.copy));
+        CU(cudaStreamWaitEvent(d.copy, d.ev_piece[2], 0));
+        CU(d2h(1, d.copy));
+        CU(d2h(2, d.stream));
+        CU(cudaStreamSynchronize(d.copy));
+    } else {
+        CU(d2h(0, d.stream));
+    }
+    d.stats.h2d_bytes += 2 * bytes; d.stats.d2h_bytes += bytes;
+    return drain(ctx, d);
 }
 
 extern "C" int herdb_eval_circuit_rows_dev(herdb_ctx* ctx, const char* session, int device, const herdb_circuit* circuit,

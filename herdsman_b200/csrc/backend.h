@@ -30,6 +30,8 @@ struct Device {
     int id = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy = nullptr;                  // second stream: uploads / downloads that ride under kernels
+    cudaEvent_t ev_piece[3] = {};
     u32 *ftw2 = nullptr, *itw1 = nullptr, *mono = nullptr;
     std::map<std::string, DeviceKey> keys;
     // scratch, grown on demand

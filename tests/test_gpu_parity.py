@@ -60,6 +60,17 @@ def test_gate_batch_sizes(backend, test_session, batch):
     assert np.array_equal(out[-k:], s["oracle"].gate("NAND", ca[-k:], cb[-k:]))
 
 
+@pytest.mark.parametrize("batch", [2368, 2369, 3001])
+def test_gate_batch_pipelined_pieces(backend, test_session, batch):
+    """from four grid rounds up the host-buffer entry point cuts the batch into head / middle / tail pieces whose
+    copies ride a second stream (backend.cpp: herdb_eval_gate_batch); every ciphertext must still equal the oracle's"""
+    s = test_session
+    a, b, ca, cb = _inputs(s, batch, seed=batch)
+    out = backend.eval_gate_batch(s["name"], "OR", ca, cb)
+    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), a | b)
+    assert np.array_equal(out, s["oracle"].gate("OR", ca, cb))
+
+
 def test_gate_empty_batch(backend, test_session):
     s = test_session
     z = np.zeros((0, s["n"] + 1), np.uint16)
