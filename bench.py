@@ -99,7 +99,9 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     sk, skr, blob = po.keygen(N_LWE, SEED)
     orc = po.Oracle(blob)
-    per_step = max(cores, args.ref_gates if args.ref_gates else 2 * cores)
+    # bounded sample: up to 16 gates per core and step (a gate costs ~40 ms on one core), fewer when many steps are
+    # asked for, so that the whole run stays near two minutes; small samples understate the CPU (thread start-up)
+    per_step = max(cores, args.ref_gates if args.ref_gates else cores * max(1, min(16, 3000 // max(1, args.steps))))
     rng = np.random.default_rng(2)
     bits_a = rng.integers(0, 2, per_step).astype(np.uint8); bits_b = rng.integers(0, 2, per_step).astype(np.uint8)
     ca = po.encrypt_bits(N_LWE, sk, bits_a, seed=2, first=0); cb = po.encrypt_bits(N_LWE, sk, bits_b, seed=2, first=1 << 24)
@@ -299,7 +301,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=0, help="gates per step per GPU (default: 32768 rounded up to whole waves of 4 x SM count)")
-    ap.add_argument("--ref-gates", type=int, default=0, help="reference arm: gates per step (default 2 x cores)")
+    ap.add_argument("--ref-gates", type=int, default=0, help="reference arm: gates per step (default up to 16 x cores)")
     ap.add_argument("--cpu-gates-per-core", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
