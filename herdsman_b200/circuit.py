@@ -243,6 +243,19 @@ def select_circuit(bits=8, basis="wire"):
     return c
 
 
+def pipeline_stages(bits=8, basis="wire"):
+    """config 5 as three chained map stages whose rows feed one another unchanged (herdb_eval_pipeline_rows):
+    (a, b, c) -> (a + b, c) -> (a + b < c, a + b, c) -> select.  Columns a later stage needs ride along as
+    pass-through outputs (no bootstrap)."""
+    t = {8: DataType.UINT8, 16: DataType.UINT16, 32: DataType.UINT32}[bits]
+    s1 = Circuit([[t, t, t]], [("s", t), ("c", t)])
+    s1.output_word(0, _ripple_add(s1, s1.input_word(0, 0), s1.input_word(0, 1), basis)); s1.output_word(1, s1.input_word(0, 2))
+    s2 = Circuit([[t, t]], [("lt", DataType.BIT), ("s", t), ("c", t)])
+    xs, ys = s2.input_word(0, 0), s2.input_word(0, 1)
+    s2.output_bit(0, 0, _less_than(s2, xs, ys, basis)); s2.output_word(1, xs); s2.output_word(2, ys)
+    return [s1, s2, select_circuit(bits, basis)]
+
+
 def pipeline_circuit(bits=8, basis="wire"):
     """config 5 fused into one map stage: (a, b, c) -> (a + b < c) ? a + b : c."""
     t = {8: DataType.UINT8, 16: DataType.UINT16, 32: DataType.UINT32}[bits]

@@ -175,13 +175,7 @@ def test_pipeline_rows_keep_intermediates_on_device(world):
     n_rows = 6
     rng = np.random.default_rng(8)
     a = rng.integers(0, 256, n_rows); b = rng.integers(0, 256, n_rows); t = rng.integers(0, 256, n_rows)
-    D = cm.DataType
-    s1 = cm.Circuit([[D.UINT8, D.UINT8, D.UINT8]], [("s", D.UINT8), ("t", D.UINT8)])
-    s1.output_word(0, cm._ripple_add(s1, s1.input_word(0, 0), s1.input_word(0, 1), "wire")); s1.output_word(1, s1.input_word(0, 2))
-    s2 = cm.Circuit([[D.UINT8, D.UINT8]], [("lt", D.BIT), ("s", D.UINT8), ("t", D.UINT8)])
-    xs, ys = s2.input_word(0, 0), s2.input_word(0, 1)
-    s2.output_bit(0, 0, cm._less_than(s2, xs, ys, "wire")); s2.output_word(1, xs); s2.output_word(2, ys)
-    s3 = cm.select_circuit(8)
+    s1, s2, s3 = cm.pipeline_stages(8)
     bits = np.concatenate([cm.pack_words(a, 8), cm.pack_words(b, 8), cm.pack_words(t, 8)], axis=1)
     rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=45)
     be = w["wg"].backend

@@ -120,6 +120,16 @@ def main():
         print(json.dumps({"config": "configs[4] add->compare->select (3 stages, host round trip between stages)", "rows": r,
                           "boot_gates_per_row": gates, "seconds": dt, "rows_per_s": r / dt, "gates_per_s": r * gates / dt,
                           "decrypt_matches_plaintext": good}), flush=True)
+        chain = cm.pipeline_stages(8)                      # same work, intermediate rows stay in HBM
+        be.eval_pipeline_rows("s", chain, abd[:64])
+        t0 = time.perf_counter()
+        out = be.eval_pipeline_rows("s", chain, abd)
+        dt = time.perf_counter() - t0
+        good = bool(np.array_equal(cm.unpack_words(api.client_decrypt_bits(N, sk, out)).reshape(r), np.where(sm < d, sm, d)))
+        ok &= good
+        print(json.dumps({"config": "configs[4] add->compare->select (3 stages, intermediate rows resident on the device)", "rows": r,
+                          "boot_gates_per_row": gates, "seconds": dt, "rows_per_s": r / dt, "gates_per_s": r * gates / dt,
+                          "decrypt_matches_plaintext": good, "bit_identical_to_staged": bool(np.array_equal(out, s3))}), flush=True)
     if "sweep" in todo:
         rng = np.random.default_rng(2)
         B = 1
