@@ -180,3 +180,66 @@ def test_rescheduled_levels_bit_exact(backend, test_session, name, build, plain)
     assert np.array_equal(out[:6], ref)
     small = backend.eval_circuit_rows(s["name"], c, rows_in[:5])                  # 5 rows: as-soon-as-possible levels
     assert np.array_equal(small, out[:5])
+
+
+def test_small_memory_budget_chunks_rows_and_batches(backend, test_session, monkeypatch):
+    """HERDB_MEM_BUDGET_MB bounds the scratch (slot file + extraction buffer): with 1 MiB an 8-bit adder runs 13 rows
+    per chunk and a gate batch 511 gates per launch.  Same ciphertexts as the unchunked run."""
+    s = test_session
+    monkeypatch.setenv("HERDB_MEM_BUDGET_MB", "1")
+    small = api.Backend(devices=(0,))
+    try:
+        small.load_key_mem("tiny", s["blob"])
+        c = cm.adder_circuit(8)
+        rows = 40
+        rng = np.random.default_rng(12)
+        x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
+        bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
+        rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=5)
+        small.reset_stats()
+        got = small.eval_circuit_rows("tiny", c, rows_in)
+        assert small.stats()["blind_rotate_launches"] > api.analyze(c)["levels"]        # really chunked
+        assert np.array_equal(got, backend.eval_circuit_rows(s["name"], c, rows_in))
+        assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], got)), (x + y) % 256)
+        a, b, ca, cb = _inputs(s, 2500, seed=3)
+        small.reset_stats()
+        out = small.eval_gate_batch("tiny", "NAND", ca, cb)
+        assert small.stats()["blind_rotate_launches"] >= 5
+        assert np.array_equal(out, backend.eval_gate_batch(s["name"], "NAND", ca, cb))
+        assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
+    finally:
+        small.close()
+
+
+def test_concurrent_callers_share_a_device(backend, test_session):
+    """the seam allows calls from several threads (executor thread + bench drivers): a device is driven by one host
+    thread at a time (Device::mu), results are what each caller would get alone"""
+    import threading
+    s = test_session
+    c = cm.adder_circuit(8)
+    rng = np.random.default_rng(14)
+    x = rng.integers(0, 256, 12); y = rng.integers(0, 256, 12)
+    rows_in = api.client_encrypt_bits(s["n"], s["sk"], np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1), seed=6)
+    a, b, ca, cb = _inputs(s, 700, seed=15)
+    want_rows = backend.eval_circuit_rows(s["name"], c, rows_in)
+    want_gate = backend.eval_gate_batch(s["name"], "AND", ca, cb)
+    got, errs = {}, []
+
+    def worker(k):
+        try:
+            for rep in range(3):
+                if k % 2:
+                    got[(k, rep)] = ("rows", backend.eval_circuit_rows(s["name"], c, rows_in))
+                else:
+                    got[(k, rep)] = ("gate", backend.eval_gate_batch(s["name"], "AND", ca, cb))
+        except Exception as e:      # noqa: BLE001
+            errs.append(e)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs and len(got) == 12
+    for kind, v in got.values():
+        assert np.array_equal(v, want_rows if kind == "rows" else want_gate)
