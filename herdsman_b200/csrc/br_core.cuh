@@ -283,9 +283,9 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                     V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys_b]);
 #pragma unroll
                     for (int p = 0; p < 4; ++p) {
-                        u32 rp = fold62(mac[c][0][jo][p]);
-                        u32 rn = fold62(mac[c][1][jo][p]);
-                        u32 y = fold62((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
+                        u32 rp = fold62_mac(mac[c][0][jo][p]);          // < 3.01 Q: the two products below stay < 2^57
+                        u32 rn = fold62_mac(mac[c][1][jo][p]);
+                        u32 y = fold62_mac((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
                         av.v[p] = canon32(av.v[p] + y);
                     }
                     *reinterpret_cast<V4*>(&S.acc[c][jo][phys_b]) = av;

@@ -134,6 +134,48 @@ HERDB_HD u32 fold62(u64 x) {
     u32 hi = (u32)(x >> 31), lo = (u32)x & 0x7FFFFFFFu;
     return mul_shoup_lazy(kR31, kR31s, hi) + lo;
 }
+// The same fold with the quotient taken on the FP64 pipe, which is otherwise idle (DFMA issues beside IMAD on
+// B200: profiles/r01m_fp64_microbench.txt).  For x < 2^62 the register pair {lo = (x >> 11) mod 2^32,
+// hi = 0x43300000 | (x >> 43)} read as a double is exactly 2^52 + floor(x / 2^11) (x >> 11 < 2^51 fits the
+// mantissa), so with M = 2^11 / Q and C = 1.5 * 2^52 - 2^52 * M
+//   qd = fma(pair, M, C) = 1.5 * 2^52 + round(x / Q) (+-1): its low word is the quotient q (mod 2^32)
+//   r  = lo32(x) - q * Q (mod 2^32) = x - q * Q exactly, |r| <= 1.001 Q
+// Two shifts, one DFMA and one IMAD replace IMAD.HI + 2 IMAD + shift + mask; the residue class is exact, only
+// the representative differs: result in [0.99 Q, 3.01 Q].
+HERDB_HD double f64_words(u32 hi, u32 lo) {
+#if defined(__CUDA_ARCH__)
+    return __hiloint2double((int)hi, (int)lo);
+#else
+    u64 b = ((u64)hi << 32) | lo; double d; __builtin_memcpy(&d, &b, 8); return d;
+#endif
+}
+HERDB_HD u32 f64_low(double d) {
+#if defined(__CUDA_ARCH__)
+    return (u32)__double2loint(d);
+#else
+    u64 b; __builtin_memcpy(&b, &d, 8); return (u32)b;
+#endif
+}
+HERDB_HD double f64_fma(double a, double b, double c) {
+#if defined(__CUDA_ARCH__)
+    return __fma_rn(a, b, c);
+#else
+    return __builtin_fma(a, b, c);
+#endif
+}
+constexpr double kTwo52d = 4503599627370496.0;
+constexpr double kFoldMd = 2048.0 / (double)kQ;
+constexpr double kFoldCd = 1.5 * kTwo52d - kTwo52d * kFoldMd;
+HERDB_HD u32 fold62_f64(u64 x) {
+    const double d = f64_words(0x43300000u | (u32)(x >> 43), (u32)(x >> 11));
+    const u32 q = f64_low(f64_fma(d, kFoldMd, kFoldCd));
+    return (u32)x - q * kQ + kQ2;
+}
+#if defined(HERDB_FOLD_INT)
+HERDB_HD u32 fold62_mac(u64 x) { return fold62(x); }
+#else
+HERDB_HD u32 fold62_mac(u64 x) { return fold62_f64(x); }
+#endif
 // exact a*b mod Q for canonical a, b (key load only; 64-bit remainder)
 HERDB_HD u32 mulmod_slow(u32 a, u32 b) { return (u32)(((u64)a * b) % kQ); }
 // Folds the four gadget rows of one (LWE index, sign, accumulator component, column, evaluation point):
