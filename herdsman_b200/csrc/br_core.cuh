@@ -9,7 +9,7 @@
 // Key switching + ModSwitch(qKS -> q) is keyswitch.cu.
 //
 // Data residency (per CTA, shared memory):
-//   acc  [kC][2][1024] u32   accumulator, NTT domain, pre-scaled by 1/N, canonical [0,Q)
+//   acc  [kC][2][1024] u32   accumulator, NTT domain, pre-scaled by 1/N, lazily reduced to [0,2Q)
 //   dig  [kC][6][1024] u32   NTT of the signed-digit polynomials l = 0,1,2 of both components, lazy residues
 //                            < 2^32; the top digit l = 3 is never transformed (top-digit elimination,
 //                            modarith.cuh): its key rows are folded so that they multiply acc itself
@@ -283,10 +283,10 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                     V4 av = *reinterpret_cast<const V4*>(&S.acc[c][jo][phys_b]);
 #pragma unroll
                     for (int p = 0; p < 4; ++p) {
-                        u32 rp = fold62_mac(mac[c][0][jo][p]);          // < 3.01 Q: the two products below stay < 2^57
-                        u32 rn = fold62_mac(mac[c][1][jo][p]);
-                        u32 y = fold62_mac((u64)mp.v[p] * rp + (u64)mn.v[p] * rn);
-                        av.v[p] = canon32(av.v[p] + y);
+                        const u32 rp = fold62_f64(mac[c][0][jo][p]);       // < 1.76 Q: the sum below stays < 2^56
+                        const u32 rn = fold62_f64(mac[c][1][jo][p]);
+                        // acc + update in (0.2499 Q, 3.7501 Q) -> [0, 2Q): what the inverse transform and the MAC accept
+                        av.v[p] = csub(fold62_f64((u64)mp.v[p] * rp + (u64)mn.v[p] * rn, av.v[p]), kQ2);
                     }
                     *reinterpret_cast<V4*>(&S.acc[c][jo][phys_b]) = av;
                 }

@@ -136,12 +136,13 @@ HERDB_HD u32 fold62(u64 x) {
 }
 // The same fold with the quotient taken on the FP64 pipe, which is otherwise idle (DFMA issues beside IMAD on
 // B200: profiles/r01m_fp64_microbench.txt).  For x < 2^62 the register pair {lo = (x >> 11) mod 2^32,
-// hi = 0x43300000 | (x >> 43)} read as a double is exactly 2^52 + floor(x / 2^11) (x >> 11 < 2^51 fits the
-// mantissa), so with M = 2^11 / Q and C = 1.5 * 2^52 - 2^52 * M
-//   qd = fma(pair, M, C) = 1.5 * 2^52 + round(x / Q) (+-1): its low word is the quotient q (mod 2^32)
-//   r  = lo32(x) - q * Q (mod 2^32) = x - q * Q exactly, |r| <= 1.001 Q
-// Two shifts, one DFMA and one IMAD replace IMAD.HI + 2 IMAD + shift + mask; the residue class is exact, only
-// the representative differs: result in [0.99 Q, 3.01 Q].
+// hi = 0x43300000 | (x >> 43)} read as a double is exactly 2^52 + y, y = floor(x / 2^11) < 2^51.  With the
+// integer ci = round(2^63 / Q) (37 bits), M = ci / 2^52 and C = 1.5 * 2^52 - ci - 1 (both exact doubles)
+//   fma(pair, M, C) = 1.5 * 2^52 + y * ci / 2^52 - 1, rounded once to an integer: its low word is q - 1
+//   (mod 2^32) with |q - x/Q| <= 0.5 (rounding) + 0.25 (ci) + 2^-16 (the 11 dropped bits), so
+//   r = lo32(x) - (q - 1) * Q (mod 2^32) = x - q * Q + Q exactly, in (0.2499 Q, 1.7501 Q).
+// Two shifts, one DFMA and one IMAD replace shift + mask + IMAD.HI + 2 IMAD + add; the residue class is exact,
+// only the representative differs from fold62's.  fold62_f64(x, a) = r + a for an addend a < 2^30.
 HERDB_HD double f64_words(u32 hi, u32 lo) {
 #if defined(__CUDA_ARCH__)
     return __hiloint2double((int)hi, (int)lo);
@@ -164,18 +165,15 @@ HERDB_HD double f64_fma(double a, double b, double c) {
 #endif
 }
 constexpr double kTwo52d = 4503599627370496.0;
-constexpr double kFoldMd = 2048.0 / (double)kQ;
-constexpr double kFoldCd = 1.5 * kTwo52d - kTwo52d * kFoldMd;
-HERDB_HD u32 fold62_f64(u64 x) {
+constexpr u64 kFoldCi = ((1ull << 63) + kQ / 2) / kQ;               // round(2^63 / Q)
+static_assert(kFoldCi < (1ull << 37), "ci = round(2^63 / Q) has 37 bits");
+constexpr double kFoldMd = (double)kFoldCi / kTwo52d;
+constexpr double kFoldCd = 1.5 * kTwo52d - (double)kFoldCi - 1.0;
+HERDB_HD u32 fold62_f64(u64 x, u32 addend = 0) {     // x < 2^62 -> addend + residue in (0.2499 Q, 1.7501 Q)
     const double d = f64_words(0x43300000u | (u32)(x >> 43), (u32)(x >> 11));
-    const u32 q = f64_low(f64_fma(d, kFoldMd, kFoldCd));
-    return (u32)x - q * kQ + kQ2;
+    const u32 q1 = f64_low(f64_fma(d, kFoldMd, kFoldCd));
+    return (u32)x + addend - q1 * kQ;
 }
-#if defined(HERDB_FOLD_INT)
-HERDB_HD u32 fold62_mac(u64 x) { return fold62(x); }
-#else
-HERDB_HD u32 fold62_mac(u64 x) { return fold62_f64(x); }
-#endif
 // exact a*b mod Q for canonical a, b (key load only; 64-bit remainder)
 HERDB_HD u32 mulmod_slow(u32 a, u32 b) { return (u32)(((u64)a * b) % kQ); }
 // Folds the four gadget rows of one (LWE index, sign, accumulator component, column, evaluation point):
