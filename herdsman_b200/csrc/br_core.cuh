@@ -209,7 +209,6 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             env.syncwarp();                                   // all lanes done reading the scratch
             // digits l = 0,1,2 (the top digit is not needed: top-digit elimination), transformed together
             u32 y[kDGT][32];
-#if defined(HERDB_PASS1_INT)
 #pragma unroll
             for (int l = 0; l < (int)kDGT; ++l)
 #pragma unroll
@@ -217,18 +216,6 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             fwd_pass1_digits_multi<(int)kDGT>(y);                 // raw digits r + 64; the offset is folded into stage 0
 #pragma unroll
             for (int l = 0; l < (int)kDGT; ++l) store_strided(S.dig[c][j + 2 * l], lane, y[l]);   // output polynomial index j + 2*l
-#else
-            // pass 1 one digit at a time, quotients on the FP64 pipe (ntt_core.cuh): the raw digits r + 64 are
-            // written straight into the low words of the register pairs
-#pragma unroll
-            for (int l = 0; l < (int)kDGT; ++l) {
-                double xd[32];
-#pragma unroll
-                for (int k = 0; k < 32; ++k) xd[k] = f64_words(0x43300000u, (d[k] >> (7 * l)) & 127u);
-                fwd_pass1_digits_f64(xd);
-                store_strided_low(S.dig[c][j + 2 * l], lane, xd);
-            }
-#endif
             env.syncwarp();
 #pragma unroll
             for (int l = 0; l < (int)kDGT; ++l) load_contig(S.dig[c][j + 2 * l], lane, y[l]);

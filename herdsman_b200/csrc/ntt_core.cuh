@@ -132,71 +132,6 @@ HERDB_HD void fwd_pass2_stream(u32 (&x)[32], const u32* lane_tw, u32 lane) {
     }
 }
 
-// ---------------------------------------------------------------- forward pass 1 with the quotients on the FP64 pipe
-// The Shoup quotient mulhi(w', y) costs two slots of the IMAD pipe; the FP64 pipe is idle and DFMA issues beside
-// IMAD (profiles/r01m_fp64_microbench.txt).  A value y < 2^32 kept as the LOW word of a register pair whose
-// high word is 0x43300000 reads as the double 2^52 + y with no instruction, and for the twiddle w with
-// ci = round(w * 2^52 / Q), c = ci / 2^52, k = 2^52 - ci (exact doubles)
-//     fma(2^52 + y, c, k) = 2^52 + y * ci / 2^52, rounded once to an integer: low word q = round(w*y/Q) (+- 2^-21)
-//     r = w*y - q*Q (mod 2^32): the SIGNED residue of w*y, |r| <= 0.5001 Q.
-// Butterfly: a' = a + r + Q, b' = a - r + Q (offsets are multiples of Q, so only the representative changes):
-// values stay non-negative and grow by at most 1.5001 Q per stage.  The data lives in the pairs for the whole
-// pass; only the low words are rewritten.
-struct F64Tw { double c, k; u32 w, pad; };
-struct UniformTw64 { F64Tw v[32]; };
-constexpr F64Tw make_f64tw(u32 w) {
-    // ci = round(w * 2^52 / Q) by two 26-bit long-division steps (everything below 2^53)
-    const u64 hi = ((u64)w << 26) / kQ, rem = ((u64)w << 26) % kQ;
-    const u64 ci = (hi << 26) + ((rem << 26) + kQ / 2) / kQ;
-    return F64Tw{(double)ci / kTwo52d, kTwo52d - (double)ci, w, 0u};
-}
-constexpr UniformTw64 make_uniform64_fwd() {
-    UniformTw64 t{};
-    for (u32 k = 1; k < 32; ++k) t.v[k] = make_f64tw(ctw_fwd(k));
-    return t;
-}
-#if defined(__CUDACC__)
-__constant__ UniformTw64 c_tw64_fwd = make_uniform64_fwd();
-#endif
-static constexpr UniformTw64 h_tw64_fwd = make_uniform64_fwd();
-#if defined(__CUDA_ARCH__)
-#define HERDB_TW64F(k) c_tw64_fwd.v[k]
-#else
-#define HERDB_TW64F(k) h_tw64_fwd.v[k]
-#endif
-HERDB_HD u32 f64_high(double d) {
-#if defined(__CUDA_ARCH__)
-    return (u32)__double2hiint(d);
-#else
-    u64 b; __builtin_memcpy(&b, &d, 8); return (u32)(b >> 32);
-#endif
-}
-HERDB_HD void bfly_f64(double& a, double& b, const F64Tw& t, u32 ka, u32 kb) {
-    const u32 y = f64_low(b);
-    const u32 q = f64_low(f64_fma(b, t.c, t.k));
-    const u32 r = t.w * y - q * kQ;
-    const u32 u = f64_low(a);
-    a = f64_words(f64_high(a), u + r + ka);
-    b = f64_words(f64_high(b), u - r + kb);
-}
-// Digit polynomial given as RAW digits u = r + 64 in [0,127] in the low words of the pairs (see fwd_pass1_digits:
-// the offset -64 is absorbed into the add constants of stage 0).  Output low words < 2.6 Q + 4 * 1.5001 Q < 8.7 Q.
-constexpr u32 kDigF1 = (kQ - 64 + kQ - cmulmod(ctw_fwd(1), 64)) % kQ + kQ;     // (-64 - 64 W1) mod Q, + Q
-constexpr u32 kDigF2 = (kQ - 64 + cmulmod(ctw_fwd(1), 64)) % kQ + kQ;          // (-64 + 64 W1) mod Q, + Q
-HERDB_HD void fwd_pass1_digits_f64(double (&xd)[32]) {
-#pragma unroll
-    for (int k = 0; k < 16; ++k) bfly_f64(xd[k], xd[k + 16], HERDB_TW64F(1), kDigF1, kDigF2);
-#pragma unroll
-    for (int s = 1; s < 5; ++s) {
-        const int h = 16 >> s;
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            if (k & h) continue;
-            bfly_f64(xd[k], xd[k + h], HERDB_TW64F((1 << s) + k / (2 * h)), kQ, kQ);
-        }
-    }
-}
-
 // M digit polynomials of the same accumulator component transformed together by one warp: M independent
 // butterflies per twiddle give the scheduler M times the instruction-level parallelism (a warp shares its
 // scheduler with only one other warp) and every streamed twiddle pair is loaded once for the M of them.
@@ -302,10 +237,6 @@ HERDB_HD void store_contig(u32* poly, u32 lane, const u32 (&x)[32]) {
 HERDB_HD void load_strided(const u32* poly, u32 lane, u32 (&x)[32]) {     // 32 x 32-bit, conflict free
 #pragma unroll
     for (int k = 0; k < 32; ++k) x[k] = poly[32 * k + ((((lane >> 2) ^ (k & 7)) << 2) | (lane & 3))];
-}
-HERDB_HD void store_strided_low(u32* poly, u32 lane, const double (&xd)[32]) {
-#pragma unroll
-    for (int k = 0; k < 32; ++k) poly[32 * k + ((((lane >> 2) ^ (k & 7)) << 2) | (lane & 3))] = f64_low(xd[k]);
 }
 HERDB_HD void store_strided(u32* poly, u32 lane, const u32 (&x)[32]) {
 #pragma unroll
