@@ -111,3 +111,8 @@ extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u1
                                 u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
     return emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
 }
+
+// the FP64-pipe fold of phase B (modarith.cuh), host form, for the range / residue property test
+extern "C" void emu_fold62_f64(const u64* x, const u32* addend, u32* out, size_t count) {
+    for (size_t i = 0; i < count; ++i) out[i] = fold62_f64(x[i], addend[i]);
+}

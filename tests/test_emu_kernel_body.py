@@ -59,3 +59,25 @@ def test_emulated_kernel_body_extreme_inputs(emu, test_key):
     for i in range(4):
         assert np.array_equal(o.blind_rotate_trace("NAND", ca[i], cb[i], n).reshape(2, 1024), trace[i])
         assert np.array_equal(o.bootstrap_extract("NAND", ca[i], cb[i]), ext[i])
+
+
+def test_fp64_fold_residue_and_range(emu):
+    """fold62_f64 (phase B): for every x < 2^62 the result is congruent to x + addend mod Q and lies in
+    addend + (0.2499 Q, 1.7501 Q) -- the bound the accumulator update and the monomial products rely on."""
+    Q = po.Q if hasattr(po, "Q") else 134215681
+    rng = np.random.default_rng(11)
+    xs = [0, 1, Q - 1, Q, Q + 1, (1 << 62) - 1, (1 << 62) - Q, (1 << 61), (1 << 43) - 1, 1 << 43, (1 << 11) - 1, 1 << 11]
+    # quotient boundaries: x/Q close to k + 1/2 (where the rounding of the DFMA decides) and to integers
+    for k in list(rng.integers(0, (1 << 62) // Q, 2000)) + [0, 1, (1 << 62) // Q - 1]:
+        k = int(k)
+        for dx in (-2, -1, 0, 1, 2):
+            xs += [k * Q + Q // 2 + dx, k * Q + dx]
+    xs += [int(v) for v in rng.integers(0, 1 << 62, 200000, dtype=np.uint64)]
+    x = np.array([v for v in xs if 0 <= v < (1 << 62)], np.uint64)
+    add = rng.integers(0, 2 * Q, x.size).astype(np.uint32); add[::3] = 0
+    out = np.zeros(x.size, np.uint32)
+    emu.emu_fold62_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+    emu.emu_fold62_f64(x.ctypes.data, add.ctypes.data, out.ctypes.data, x.size)
+    r = out.astype(np.int64) - add.astype(np.int64)
+    assert np.array_equal(r % Q, (x % np.uint64(Q)).astype(np.int64))
+    assert r.min() > 0.2499 * Q and r.max() < 1.7501 * Q
