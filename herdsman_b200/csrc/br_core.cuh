@@ -212,8 +212,8 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 #pragma unroll
             for (int l = 0; l < (int)kDGT; ++l)
 #pragma unroll
-                for (int k = 0; k < 32; ++k) y[l][k] = (d[k] >> (7 * l)) & 127u;
-            fwd_pass1_digits_multi<(int)kDGT>(y);                 // raw digits r + 64; the offset is folded into stage 0
+                for (int k = 0; k < 32; ++k) y[l][k] = d[k] & (127u << (7 * l));   // the field in place: (r_l + 64) * 2^(7l)
+            fwd_pass1_fields_multi<(int)kDGT>(y);                 // offset folded into stage 0, 2^(-7l) into the key rows
 #pragma unroll
             for (int l = 0; l < (int)kDGT; ++l) store_strided(S.dig[c][j + 2 * l], lane, y[l]);   // output polynomial index j + 2*l
             env.syncwarp();

@@ -178,13 +178,14 @@ HERDB_HD u32 fold62_f64(u64 x, u32 addend = 0) {     // x < 2^62 -> addend + res
 HERDB_HD u32 mulmod_slow(u32 a, u32 b) { return (u32)(((u64)a * b) % kQ); }
 // Folds the four gadget rows of one (LWE index, sign, accumulator component, column, evaluation point):
 // in  k[l] = K_l / N   (canonical; what the forward transform of the key load produces)
-// out k[l] = (K_l - B^(l-3) K_3) / N for l < 3,  k[3] = B^-3 * K_3  (NOT divided by N: it multiplies the
-//     stored accumulator, which already carries the 1/N)
+// out k[l] = B^-l * (K_l - B^(l-3) K_3) / N for l < 3,  k[3] = B^-3 * K_3  (NOT divided by N: it multiplies the
+//     stored accumulator, which already carries the 1/N).  The B^-l is there because phase A transforms the
+//     digit fields in place, B^l * r_l (ntt_core.cuh, fwd_pass1_fields_multi): no shift in the digit extraction.
 HERDB_HD void fold_top_digit(u32 (&k)[4]) {
     const u32 t = k[3];
     k[0] = csub(k[0] + kQ - mulmod_slow(t, kBGInv3), kQ);
-    k[1] = csub(k[1] + kQ - mulmod_slow(t, kBGInv2), kQ);
-    k[2] = csub(k[2] + kQ - mulmod_slow(t, kBGInv1), kQ);
+    k[1] = mulmod_slow(csub(k[1] + kQ - mulmod_slow(t, kBGInv2), kQ), kBGInv1);
+    k[2] = mulmod_slow(csub(k[2] + kQ - mulmod_slow(t, kBGInv1), kQ), kBGInv2);
     k[3] = mulmod_slow(mulmod_slow(t, kN % kQ), kBGInv3);
 }
 // bank-conflict-free layout of a 1024-word polynomial in shared memory: word x lives at

@@ -163,6 +163,46 @@ HERDB_HD void fwd_pass1_digits_multi(u32 (&x)[M][32]) {
         }
     }
 }
+// The same with digit l given IN PLACE: x[l][k] = (r_l + 64) * 2^(7l), the 7-bit field of the decomposed value
+// masked but not shifted down.  The transform is linear, so the warp computes 2^(7l) * NTT(r_l); the factor
+// 2^(-7l) sits in the folded key rows (fold_top_digit).  Saves the shift of every digit extraction; the offset
+// 64 * 2^(7l) goes into the add constants of stage 0 as before.  Inputs < 2^21, outputs < 3Q + 2^21 + 8Q.
+constexpr u32 dig_field_c(int l) { return kQ - (u32)((64ull << (7 * l)) % kQ); }
+constexpr u32 dig_field_k1(int l) { return (dig_field_c(l) + cmulmod(ctw_fwd(1), dig_field_c(l))) % kQ; }
+constexpr u32 dig_field_k2(int l) { return (dig_field_c(l) + kQ - cmulmod(ctw_fwd(1), dig_field_c(l))) % kQ + kQ2; }
+constexpr u32 kDigF1_0 = dig_field_k1(0), kDigF1_1 = dig_field_k1(1), kDigF1_2 = dig_field_k1(2);
+constexpr u32 kDigF2_0 = dig_field_k2(0), kDigF2_1 = dig_field_k2(1), kDigF2_2 = dig_field_k2(2);
+template <int M>
+HERDB_HD void fwd_pass1_fields_multi(u32 (&x)[M][32]) {
+    static_assert(M <= 3, "fields of digits 0..2");
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            const u32 k1 = m == 0 ? kDigF1_0 : m == 1 ? kDigF1_1 : kDigF1_2;
+            const u32 k2 = m == 0 ? kDigF2_0 : m == 1 ? kDigF2_1 : kDigF2_2;
+            u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[m][k + 16]);
+            u32 u = x[m][k];
+            x[m][k] = u + v + k1;
+            x[m][k + 16] = u - v + k2;
+        }
+#pragma unroll
+    for (int s = 1; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[m][k + h]);
+                u32 u = x[m][k];
+                x[m][k] = u + v;
+                x[m][k + h] = u - v + kQ2;
+            }
+        }
+    }
+}
 template <int M>
 HERDB_HD void fwd_pass2_stream_multi(u32 (&x)[M][32], const u32* lane_tw, u32 lane) {
     int off = 0;
