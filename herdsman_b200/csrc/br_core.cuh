@@ -190,11 +190,11 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             const int c = warp >> 1, j = warp & 1;
             u32 x[32];
             load_contig(S.acc[c][j], lane, x);
-            inv_pass1(x, S.itw, lane);
+            inv_pass1<1, 2>(x, S.itw, lane);
             store_contig(S.dig[c][j], lane, x);              // dig[c][j] doubles as transposition scratch
             env.syncwarp();
             load_strided(S.dig[c][j], lane, x);
-            inv_pass2(x);
+            inv_pass2<2, 1>(x);
             // SignedDigitDecompose.  d = centred representative of the coefficient; OpenFHE peels signed
             // 7-bit digits r_l in [-64,63] iteratively.  Equivalently d + B = sum (r_l + 64) * 128^l with
             // B = 64*(1 + 128 + 128^2 + 128^3): the digits are the plain 7-bit fields of d + B (unique
@@ -301,11 +301,11 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
         const u32 job = group * kC + c;
         u32 x[32];
         load_contig(S.acc[c][j], lane, x);
-        inv_pass1(x, S.itw, lane);
+        inv_pass1<1, 2>(x, S.itw, lane);
         store_contig(S.dig[c][j], lane, x);
         env.syncwarp();
         load_strided(S.dig[c][j], lane, x);
-        inv_pass2(x);
+        inv_pass2<2, 1>(x);
         if (job < P.jobs) {
             u16* ext = P.ext + (size_t)job * kExtStride;
 #pragma unroll

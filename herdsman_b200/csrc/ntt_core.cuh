@@ -227,8 +227,25 @@ HERDB_HD void fwd_pass2_stream_multi(u32 (&x)[M][32], const u32* lane_tw, u32 la
     }
 }
 
-// ---------------------------------------------------------------- inverse (GS): invariant all values in [0, 2Q)
+// ---------------------------------------------------------------- inverse (GS), statically lazy
+// Every value carries a compile-time bound b (in units of 2Q: value < b * 2Q).  A butterfly (u, v) -> (u + v,
+// w * (u - v + b_v * 2Q)) gives the sum the bound b_u + b_v and RESETS the product to 1 (Shoup takes any
+// multiplicand below 2^32 and returns [0, 2Q)).  A conditional subtraction csub(x, m * 2Q), m = ceil(b / 2),
+// halves a bound and is spent only where the next sum would pass 16 units (32 Q < 2^32) or where the caller's
+// output bound demands it: an element that becomes a product before its bound matters never pays.  Everything
+// is unrolled, so the bounds are constants and only the needed corrections are emitted: 16 + 36 per
+// polynomial for the two passes (bounds 1 -> 2 -> 1) instead of 80 + 80 with the invariant [0, 2Q).
+constexpr int kInvBoundMax = 16;
+HERDB_HD void inv_reduce_to(u32& x, int& b, int lim) {        // at most four halvings: 16 -> 1
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        if (b > lim) { const int m = (b + 1) / 2; x = csub(x, (u32)m * kQ2); b = m; }
+}
+template <int B0, int BOUT>
 HERDB_HD void inv_pass1(u32 (&x)[32], const u32* lane_tw /* smem or global, chunked [g][32][4] */, u32 lane) {
+    int b[32];
+#pragma unroll
+    for (int e = 0; e < 32; ++e) b[e] = B0;
     int off = 0;
 #pragma unroll
     for (int t = 1; t <= 16; t <<= 1) {
@@ -238,13 +255,20 @@ HERDB_HD void inv_pass1(u32 (&x)[32], const u32* lane_tw /* smem or global, chun
             const int p = off + e / (2 * t);
             const u32* tp = lane_tw + ((p >> 1) * 32 + lane) * 4 + (p & 1) * 2;
             u32 u = x[e], v = x[e + t];
-            x[e] = csub(u + v, kQ2);
-            x[e + t] = mul_shoup_lazy(tp[0], tp[1], u - v + kQ2);
+            x[e] = u + v;
+            x[e + t] = mul_shoup_lazy(tp[0], tp[1], u - v + (u32)b[e + t] * kQ2);
+            b[e] += b[e + t];
+            b[e + t] = 1;
+            inv_reduce_to(x[e], b[e], t == 16 ? BOUT : kInvBoundMax / 2);
         }
         off += 16 / t;
     }
 }
+template <int B0, int BOUT>
 HERDB_HD void inv_pass2(u32 (&x)[32]) {           // strided layout, strides 32..512
+    int b[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) b[k] = B0;
 #pragma unroll
     for (int h = 1; h <= 16; h <<= 1) {
 #pragma unroll
@@ -252,8 +276,11 @@ HERDB_HD void inv_pass2(u32 (&x)[32]) {           // strided layout, strides 32.
             if (k & h) continue;
             const int idx = 16 / h + k / (2 * h);
             u32 u = x[k], v = x[k + h];
-            x[k] = csub(u + v, kQ2);
-            x[k + h] = mul_shoup_lazy(HERDB_TWI(idx, 0), HERDB_TWI(idx, 1), u - v + kQ2);
+            x[k] = u + v;
+            x[k + h] = mul_shoup_lazy(HERDB_TWI(idx, 0), HERDB_TWI(idx, 1), u - v + (u32)b[k + h] * kQ2);
+            b[k] += b[k + h];
+            b[k + h] = 1;
+            inv_reduce_to(x[k], b[k], h == 16 ? BOUT : kInvBoundMax / 2);
         }
     }
 }

@@ -24,11 +24,11 @@ struct Smem {
 __device__ __forceinline__ void phase_a(Smem& S, int c, int j, u32 lane) {
     u32 x[32];
     load_contig(S.acc[c][j], lane, x);
-    inv_pass1(x, S.itw, lane);
+    inv_pass1<1, 2>(x, S.itw, lane);
     store_contig(S.dig[c][j], lane, x);
     __syncwarp();
     load_strided(S.dig[c][j], lane, x);
-    inv_pass2(x);
+    inv_pass2<2, 1>(x);
     constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
     u32 y[kDGT][32];
 #pragma unroll

@@ -30,11 +30,11 @@ __global__ void __launch_bounds__(256, 1) k(const u32* ftw_g, const u32* itw_g, 
     for (int it = 0; it < iters; ++it) {
         u32 x[32];
         load_contig(S.acc[c][j], lane, x);
-        inv_pass1(x, S.itw, lane);
+        inv_pass1<1, 2>(x, S.itw, lane);
         store_contig(S.dig[c][j], lane, x);
         __syncwarp();
         load_strided(S.dig[c][j], lane, x);
-        inv_pass2(x);
+        inv_pass2<2, 1>(x);
         constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
         u32 d[32];
 #pragma unroll
@@ -151,11 +151,11 @@ __global__ void __launch_bounds__(512, 1) k16(const u32* ftw_g, const u32* itw_g
         u32 x[32];
         u32* scratch = S.dig[c][j + 4 * h];
         load_contig(S.acc[c][j], lane, x);
-        inv_pass1(x, S.itw, lane);
+        inv_pass1<1, 2>(x, S.itw, lane);
         store_contig(scratch, lane, x);
         __syncwarp();
         load_strided(scratch, lane, x);
-        inv_pass2(x);
+        inv_pass2<2, 1>(x);
         constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
         u32 d[32];
 #pragma unroll

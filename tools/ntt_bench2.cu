@@ -31,11 +31,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) k(const u32* ftw_g, const u32* 
         u32 x[32];
         load_contig(S.acc[c][j], lane, x);
         if (!(REGCAP & 2)) {
-            inv_pass1(x, S.itw, lane);
+            inv_pass1<1, 2>(x, S.itw, lane);
             store_contig(S.dig[c][j], lane, x);
             __syncwarp();
             load_strided(S.dig[c][j], lane, x);
-            inv_pass2(x);
+            inv_pass2<2, 1>(x);
         }
         constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
         u32 d[32];
@@ -93,11 +93,11 @@ __global__ void __launch_bounds__(384, 1) k_helper(const u32* ftw_g, const u32* 
             const int c = warp >> 1, j = warp & 1;
             u32 x[32];
             load_contig(S.acc[c][j], lane, x);
-            inv_pass1(x, S.itw, lane);
+            inv_pass1<1, 2>(x, S.itw, lane);
             store_contig(S.dig[c][j], lane, x);
             __syncwarp();
             load_strided(S.dig[c][j], lane, x);
-            inv_pass2(x);
+            inv_pass2<2, 1>(x);
             constexpr u32 kB = 64u * (1u + 128u + 128u * 128u + 128u * 128u * 128u);
             u32 y[2][32];
 #pragma unroll
