@@ -89,6 +89,11 @@ constexpr UniformTw make_uniform_fwd() {
     for (u32 k = 1; k < 32; ++k) { t.v[k][0] = ctw_fwd(k); t.v[k][1] = cshoup(t.v[k][0]); }
     return t;
 }
+constexpr UniformTw make_uniform_fwd_up() {      // ceiling companions ceil(w * 2^32 / Q) = w' + 1 (centred butterflies, ntt_core.cuh)
+    UniformTw t{};
+    for (u32 k = 1; k < 32; ++k) { t.v[k][0] = ctw_fwd(k); t.v[k][1] = cshoup(t.v[k][0]) + 1u; }
+    return t;
+}
 constexpr UniformTw make_uniform_inv() {
     UniformTw t{};
     for (u32 k = 1; k < 32; ++k) { t.v[k][0] = ctw_inv(k); t.v[k][1] = cshoup(t.v[k][0]); }
@@ -97,14 +102,18 @@ constexpr UniformTw make_uniform_inv() {
 #if defined(__CUDACC__)
 __constant__ UniformTw c_tw_fwd = make_uniform_fwd();
 __constant__ UniformTw c_tw_inv = make_uniform_inv();
+__constant__ UniformTw c_tw_fwd_up = make_uniform_fwd_up();
 #endif
 static constexpr UniformTw h_tw_fwd = make_uniform_fwd();
 static constexpr UniformTw h_tw_inv = make_uniform_inv();
+static constexpr UniformTw h_tw_fwd_up = make_uniform_fwd_up();
 
 #if defined(__CUDA_ARCH__)
 #define HERDB_TWF(k, i) c_tw_fwd.v[k][i]
 #define HERDB_TWI(k, i) c_tw_inv.v[k][i]
+#define HERDB_TWFU(k, i) c_tw_fwd_up.v[k][i]
 #else
+#define HERDB_TWFU(k, i) h_tw_fwd_up.v[k][i]
 #define HERDB_TWF(k, i) h_tw_fwd.v[k][i]
 #define HERDB_TWI(k, i) h_tw_inv.v[k][i]
 #endif

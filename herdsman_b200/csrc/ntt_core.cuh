@@ -167,6 +167,21 @@ HERDB_HD void fwd_pass1_digits_multi(u32 (&x)[M][32]) {
 // masked but not shifted down.  The transform is linear, so the warp computes 2^(7l) * NTT(r_l); the factor
 // 2^(-7l) sits in the folded key rows (fold_top_digit).  Saves the shift of every digit extraction; the offset
 // 64 * 2^(7l) goes into the add constants of stage 0 as before.  Inputs < 2^21, outputs < 3Q + 2^21 + 8Q.
+// Centred forward butterfly, four instructions instead of five.  With the CEILING companion w'' = ceil(w * 2^32 / Q)
+// = w' + 1 the quotient q = mulhi(w'', y) is floor(w*y/Q) or one more (w''*y/2^32 - w*y/Q lies in [0, 1) for every
+// y < 2^32), so the Shoup remainder rho = w*y - q*Q lies in [-Q, Q) instead of [0, 2Q) and the difference needs
+// no offset:  x' = (w*y + u) - q*Q = u + rho  (two IMADs, u as the addend of the first),  y' = u + u - x' = u - rho
+// (ONE three-input add).  Every stage widens the range of the values by Q on either side; stage 0 of the digit
+// transforms starts them at 11 Q (add constants), so after ten stages they lie in [Q, 22 Q + 2^21): non-negative,
+// below 2^32, same upper bound as the [0, 2Q) form.  Ceiling companions: c_tw_fwd_up for the uniform stages, the
+// lane table in shared memory gets its +1 when the CTA copies it (br_core.cuh).
+HERDB_HD void bfly_fwd_centred(u32& a, u32& b, u32 w, u32 wpu) {
+    const u32 q = mulhi32(wpu, b);
+    const u32 xn = w * b + a - q * kQ;
+    b = a + a - xn;
+    a = xn;
+}
+constexpr u32 kFwdStart = 11u * kQ;      // offset of the values after stage 0 (a multiple of Q: invisible mod Q)
 constexpr u32 dig_field_c(int l) { return kQ - (u32)((64ull << (7 * l)) % kQ); }
 constexpr u32 dig_field_k1(int l) { return (dig_field_c(l) + cmulmod(ctw_fwd(1), dig_field_c(l))) % kQ; }
 constexpr u32 dig_field_k2(int l) { return (dig_field_c(l) + kQ - cmulmod(ctw_fwd(1), dig_field_c(l))) % kQ + kQ2; }
@@ -183,8 +198,13 @@ HERDB_HD void fwd_pass1_fields_multi(u32 (&x)[M][32]) {
             const u32 k2 = m == 0 ? kDigF2_0 : m == 1 ? kDigF2_1 : kDigF2_2;
             u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[m][k + 16]);
             u32 u = x[m][k];
+#if defined(HERDB_FWD_LAZY2Q)
             x[m][k] = u + v + k1;
             x[m][k + 16] = u - v + k2;
+#else
+            x[m][k] = u + v + (k1 + kFwdStart - kQ);          // v - Q in [-Q, Q): values in [10 Q, 13 Q + 2^21)
+            x[m][k + 16] = u - v + (k2 - kQ2 + kFwdStart + kQ);
+#endif
         }
 #pragma unroll
     for (int s = 1; s < 5; ++s) {
@@ -195,14 +215,19 @@ HERDB_HD void fwd_pass1_fields_multi(u32 (&x)[M][32]) {
             const int idx = (1 << s) + k / (2 * h);
 #pragma unroll
             for (int m = 0; m < M; ++m) {
+#if defined(HERDB_FWD_LAZY2Q)
                 u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[m][k + h]);
                 u32 u = x[m][k];
                 x[m][k] = u + v;
                 x[m][k + h] = u - v + kQ2;
+#else
+                bfly_fwd_centred(x[m][k], x[m][k + h], HERDB_TWFU(idx, 0), HERDB_TWFU(idx, 1));
+#endif
             }
         }
     }
 }
+// (in the centred form `lane_tw` must hold the CEILING companions)
 template <int M>
 HERDB_HD void fwd_pass2_stream_multi(u32 (&x)[M][32], const u32* lane_tw, u32 lane) {
     int off = 0;
@@ -217,10 +242,14 @@ HERDB_HD void fwd_pass2_stream_multi(u32 (&x)[M][32], const u32* lane_tw, u32 la
             const u32 w = tp[0], wp = tp[1];
 #pragma unroll
             for (int m = 0; m < M; ++m) {
+#if defined(HERDB_FWD_LAZY2Q)
                 u32 v = mul_shoup_lazy(w, wp, x[m][e + t]);
                 u32 u = x[m][e];
                 x[m][e] = u + v;
                 x[m][e + t] = u - v + kQ2;
+#else
+                bfly_fwd_centred(x[m][e], x[m][e + t], w, wp);
+#endif
             }
         }
         off += 16 / t;
