@@ -231,6 +231,9 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
         env.sync();
         // ===== phase B: thread = kChunks chunks of 4 evaluation points: 4*(tid + q*kThreads) ..+3
         {
+            // exactness of the 64-bit sums: six digit transforms below kFwdOutMax and the two accumulator components
+            // below 2Q, each times a key word below Q, stay below 2^62 (what fold62_f64 accepts)
+            static_assert((6 * kFwdOutMax + 2 * 2ull * kQ) < ((1ull << 62) / kQ), "key MAC fits 62 bits");
             u64 mac[kC][2][2][4];
 #pragma unroll
             for (int c = 0; c < kC; ++c)

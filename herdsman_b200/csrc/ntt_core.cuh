@@ -182,6 +182,10 @@ HERDB_HD void bfly_fwd_centred(u32& a, u32& b, u32 w, u32 wpu) {
     a = xn;
 }
 constexpr u32 kFwdStart = 11u * kQ;      // offset of the values after stage 0 (a multiple of Q: invisible mod Q)
+// ranges of a digit transform: after stage 0 in [kFwdStart - Q, kFwdStart + 2Q + 2^21), nine more stages of +-Q
+constexpr u64 kFwdOutMin = (u64)kFwdStart - 10ull * kQ;
+constexpr u64 kFwdOutMax = (u64)kFwdStart + 11ull * kQ + (1ull << 21);       // exclusive
+static_assert(kFwdStart >= 10ull * kQ && kFwdOutMax < (1ull << 32), "digit transforms stay non-negative and below 2^32");
 constexpr u32 dig_field_c(int l) { return kQ - (u32)((64ull << (7 * l)) % kQ); }
 constexpr u32 dig_field_k1(int l) { return (dig_field_c(l) + cmulmod(ctw_fwd(1), dig_field_c(l))) % kQ; }
 constexpr u32 dig_field_k2(int l) { return (dig_field_c(l) + kQ - cmulmod(ctw_fwd(1), dig_field_c(l))) % kQ + kQ2; }
