@@ -47,7 +47,7 @@ struct GateDesc {
 struct Pool { u16* base; u32 row_cts; u32 pad; };    // ciphertext (r, idx) at base + (r*row_cts + idx)*(n+1)
 
 struct BrParams {
-    const u32* bsk;              // [n][2 sign][8 rows][2 cols][1024]  NTT domain, canonical, rows folded by fold_top_digit
+    const u32* bsk;              // [n][2 sign][8 rows][2 cols][1024]  NTT domain, canonical, rows folded by fold_top_digit, words at key_pos
     const u32* mono;             // [1024][1024]   NTT(X^(2*row) - 1), canonical
     const u32* ftw2;             // [16][32][4]    forward pass-2 lane twiddles
     const u32* itw1;             // [16][32][4]    inverse pass-1 lane twiddles
@@ -271,7 +271,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 #pragma unroll
                         for (int jo = 0; jo < 2; ++jo)
 #pragma unroll
-                            for (int p = 0; p < 4; ++p) mac[c][s][jo][p] += (u64)dv.v[p] * kv[s][jo].v[p];
+                            for (int p = 0; p < 4; ++p) mac[c][s][jo][p] += (u64)dv.v[p] * kv[s][jo].v[(p + 3) & 3];   // key words are stored rotated: key_pos
                 }
                 // digit r is consumed: its slots (and the ring stage it came from) take the next pieces.  The
                 // asm operands make the copies wait for this iteration's shared-memory reads (dep, kv).

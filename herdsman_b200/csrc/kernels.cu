@@ -167,17 +167,23 @@ __global__ void __launch_bounds__(256) bsk_convert_kernel(const u32* __restrict_
 // key load, second pass (in place): folds the four gadget rows of every (i, sign, component, column, point)
 // for the top-digit elimination (modarith.cuh, fold_top_digit)
 __global__ void __launch_bounds__(256) bsk_fold_kernel(u32* __restrict__ bsk, u32 n) {
-    const size_t total = (size_t)n * 2 * 2 * 2 * kN;                 // (i, sign, component j, column, point)
+    // one thread per aligned group of four points: the folded words are written back rotated (key_pos, modarith.cuh)
+    const size_t total = (size_t)n * 2 * 2 * 2 * (kN / 4);          // (i, sign, component j, column, group)
     for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
-        const u32 x = (u32)(t % kN);
-        const u32 col = (u32)(t / kN) & 1u, j = (u32)(t / (2 * kN)) & 1u;
-        const size_t is = t / (4 * kN);                                // i * 2 + sign
-        u32 k[4];
+        const u32 g = (u32)(t % (kN / 4));
+        const u32 col = (u32)(t / (kN / 4)) & 1u, j = (u32)(t / (2 * (kN / 4))) & 1u;
+        const size_t is = t / (4 * (kN / 4));                          // i * 2 + sign
+        u32 k[4][4];
 #pragma unroll
-        for (u32 l = 0; l < 4; ++l) k[l] = bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x];
-        fold_top_digit(k);
+        for (u32 p = 0; p < 4; ++p) {
 #pragma unroll
-        for (u32 l = 0; l < 4; ++l) bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x] = k[l];
+            for (u32 l = 0; l < 4; ++l) k[p][l] = bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + 4 * g + p];
+            fold_top_digit(k[p]);
+        }
+#pragma unroll
+        for (u32 p = 0; p < 4; ++p)
+#pragma unroll
+            for (u32 l = 0; l < 4; ++l) bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + key_pos(4 * g + p)] = k[p][l];
     }
 }
 

@@ -79,6 +79,11 @@ static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, cons
                     fold_top_digit(k);
                     for (u32 l = 0; l < 4; ++l) bsk[((is * kDG2 + j + 2 * l) * 2 + col) * kN + x] = k[l];
                 }
+    {   // the four points of an aligned group are stored rotated by one word (key_pos, modarith.cuh)
+        std::vector<u32> tmp(bsk);
+        for (size_t p = 0; p < polys; ++p)
+            for (u32 x = 0; x < kN; ++x) bsk[p * kN + key_pos(x)] = tmp[p * kN + x];
+    }
     std::vector<u32> mono; build_monomial_table(mono);
     std::vector<u32> ftw2(kLaneTwWords), itw1(kLaneTwWords);
     build_lane_twiddles(ftw2.data(), itw1.data());
