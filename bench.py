@@ -130,6 +130,7 @@ def run_reference(args, rank, world):
 def run_ours(args, rank, world, local_rank):
     import torch
     from herdsman_b200 import api
+    import clientsim as cs
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -140,10 +141,10 @@ def run_ours(args, rank, world, local_rank):
     be = api.Backend(devices=(local_rank,))          # raises without a CUDA device: no CPU fallback
 
     # ---- keys: generated once (client stand-in) on rank 0, broadcast over NVLink (NCCL), converted on each GPU
-    blob_size = api.lib().herdb_client_key_blob_size(N_LWE)
+    blob_size = api.lib().herdb_key_blob_size(N_LWE)
     sk = np.zeros(N_LWE, np.int8)
     if rank == 0:
-        sk, skr, blob = api.client_keygen(N_LWE, SEED)
+        sk, skr, blob = cs.keygen(N_LWE, SEED)
         d_blob = torch.from_numpy(blob).to(dev)
     else:
         d_blob = torch.empty(blob_size, dtype=torch.uint8, device=dev)
@@ -164,8 +165,8 @@ def run_ours(args, rank, world, local_rank):
     bits_a = rng.integers(0, 2, B).astype(np.uint8); bits_b = rng.integers(0, 2, B).astype(np.uint8)
     h_a = torch.empty((B, w), dtype=torch.uint16, pin_memory=True); h_b = torch.empty_like(h_a).pin_memory()
     h_out = torch.empty((B, w), dtype=torch.uint16, pin_memory=True)
-    api.client_encrypt_bits(N_LWE, sk, bits_a, seed=2 + rank, first=0, out=h_a.numpy())
-    api.client_encrypt_bits(N_LWE, sk, bits_b, seed=2 + rank, first=1 << 24, out=h_b.numpy())
+    cs.encrypt_bits(N_LWE, sk, bits_a, seed=2 + rank, first=0, out=h_a.numpy())
+    cs.encrypt_bits(N_LWE, sk, bits_b, seed=2 + rank, first=1 << 24, out=h_b.numpy())
     d_a = h_a.to(dev); d_b = h_b.to(dev); d_out = torch.zeros((B, w), dtype=torch.uint16, device=dev)
     ext = torch.cuda.ExternalStream(be.stream(), device=dev)
 
@@ -209,8 +210,8 @@ def run_ours(args, rank, world, local_rank):
     ms_e2e = timed(e2e_step, args.steps)
 
     # correctness of what was timed: every output decrypts to NAND of the inputs
-    ok_dev = np.array_equal(api.client_decrypt_bits(N_LWE, sk, d_out.cpu().numpy()), 1 - (bits_a & bits_b))
-    ok_e2e = np.array_equal(api.client_decrypt_bits(N_LWE, sk, h_out.numpy()), 1 - (bits_a & bits_b))
+    ok_dev = np.array_equal(cs.decrypt_bits(N_LWE, sk, d_out.cpu().numpy()), 1 - (bits_a & bits_b))
+    ok_e2e = np.array_equal(cs.decrypt_bits(N_LWE, sk, h_out.numpy()), 1 - (bits_a & bits_b))
     if not (ok_dev and ok_e2e):
         raise SystemExit("bench: decrypted outputs do not match NAND of the inputs")
     if dist is not None:
@@ -278,12 +279,12 @@ def cpu_baseline(be, sk, args):
     from herdsman_b200 import api
     from oracle import pyoracle as po
     cores = os.cpu_count() or 1
-    _, _, blob = api.client_keygen(N_LWE, SEED)
+    _, _, blob = cs.keygen(N_LWE, SEED)
     orc = po.Oracle(blob)
     cnt = cores * args.cpu_gates_per_core
     rng = np.random.default_rng(7)
     a = rng.integers(0, 2, cnt).astype(np.uint8); b = rng.integers(0, 2, cnt).astype(np.uint8)
-    ca = api.client_encrypt_bits(N_LWE, sk, a, seed=77, first=0); cb = api.client_encrypt_bits(N_LWE, sk, b, seed=77, first=1 << 24)
+    ca = cs.encrypt_bits(N_LWE, sk, a, seed=77, first=0); cb = cs.encrypt_bits(N_LWE, sk, b, seed=77, first=1 << 24)
     orc.gate("NAND", ca[:cores], cb[:cores], threads=cores)
     t0 = time.perf_counter()
     ref = orc.gate("NAND", ca, cb, threads=cores)

@@ -1,7 +1,9 @@
 // client.cpp -- synthetic stand-in for the herd client (libherd, not in the reference tree):
 // key generation, bit encryption and decryption in the flat formats of herdb_params.h.
-// Host only, NOT on the evaluation path: herdsman never sees secret keys; these exist so that
-// benchmarks and tests have keys and encrypted rows to feed the backend.
+// TEST / BENCH INFRASTRUCTURE ONLY, built into its own library (clientsim/libherdclientsim.so), not
+// into libherdb.so: herdsman never sees secret keys, the generator is a counter-based mixer seeded
+// with 64 bits (NOT a CSPRNG), and the flat key / row formats are this repo's own, not the
+// OpenFHE-serialised objects a real herd client uploads ("Formats").
 //
 // Follows OpenFHE binfhe v1.0.x KeyGen / KeySwitchGen / KeyGenCGGI / Encrypt / Decrypt
 // (lwe-pke.cpp, rgsw-acc-cggi.cpp) with the deterministic generator of herdb_params.h in
@@ -9,8 +11,8 @@
 // produce identical blobs from the same seed.
 #include <cstring>
 #include <vector>
-#include "../../include/herdb.h"
-#include "modarith.cuh"
+#include "herd_clientsim.h"
+#include "../herdsman_b200/csrc/modarith.cuh"
 
 namespace {
 using namespace herdb;
@@ -72,13 +74,13 @@ struct HostNtt {
 
 extern "C" {
 
-size_t herdb_client_key_blob_size(uint32_t n) {
+size_t clientsim_key_blob_size(uint32_t n) {
     return sizeof(herdb_key_header) + (size_t)n * 2 * kDG2 * 2 * kN * 4 + (size_t)kN * kBaseKS * kDKS * (n + 1) * 2;
 }
 
-int herdb_client_keygen(uint32_t n, uint64_t seed, int8_t* sk_lwe, int8_t* sk_ring, void* blob, size_t blob_len) {
-    if (!sk_lwe || !sk_ring || !blob || n == 0 || n > HERDB_N_STD128) return HERDB_ERR_ARG;
-    if (blob_len < herdb_client_key_blob_size(n)) return HERDB_ERR_ARG;
+int clientsim_keygen(uint32_t n, uint64_t seed, int8_t* sk_lwe, int8_t* sk_ring, void* blob, size_t blob_len) {
+    if (!sk_lwe || !sk_ring || !blob || n == 0 || n > HERDB_N_STD128) return -1;
+    if (blob_len < clientsim_key_blob_size(n)) return -1;
     const HostNtt ntt;
     herdb_key_header h;
     memset(&h, 0, sizeof h);
@@ -133,12 +135,12 @@ int herdb_client_keygen(uint32_t n, uint64_t seed, int8_t* sk_lwe, int8_t* sk_ri
         }
         a[n] = (u16)(((b % (int64_t)kQKS) + kQKS) % kQKS);
     }
-    return HERDB_OK;
+    return 0;
 }
 
-int herdb_client_encrypt_bits(uint32_t n, const int8_t* sk_lwe, uint64_t seed, uint64_t first_ct_index,
+int clientsim_encrypt_bits(uint32_t n, const int8_t* sk_lwe, uint64_t seed, uint64_t first_ct_index,
                               const uint8_t* bits, size_t count, uint16_t* cts) {
-    if (!sk_lwe || !bits || !cts || n == 0 || n > HERDB_N_STD128) return HERDB_ERR_ARG;
+    if (!sk_lwe || !bits || !cts || n == 0 || n > HERDB_N_STD128) return -1;
 #pragma omp parallel for schedule(static)
     for (long c = 0; c < (long)count; ++c) {
         u16* ct = cts + (size_t)c * (n + 1);
@@ -150,11 +152,11 @@ int herdb_client_encrypt_bits(uint32_t n, const int8_t* sk_lwe, uint64_t seed, u
         }
         ct[n] = (u16)(((b % (int64_t)kLweQ) + kLweQ) % kLweQ);
     }
-    return HERDB_OK;
+    return 0;
 }
 
-int herdb_client_decrypt_bits(uint32_t n, const int8_t* sk_lwe, const uint16_t* cts, size_t count, uint8_t* bits) {
-    if (!sk_lwe || !bits || !cts || n == 0 || n > HERDB_N_STD128) return HERDB_ERR_ARG;
+int clientsim_decrypt_bits(uint32_t n, const int8_t* sk_lwe, const uint16_t* cts, size_t count, uint8_t* bits) {
+    if (!sk_lwe || !bits || !cts || n == 0 || n > HERDB_N_STD128) return -1;
 #pragma omp parallel for schedule(static)
     for (long c = 0; c < (long)count; ++c) {
         const u16* ct = cts + (size_t)c * (n + 1);
@@ -164,7 +166,7 @@ int herdb_client_decrypt_bits(uint32_t n, const int8_t* sk_lwe, const uint16_t* 
         const u32 rr = (u32)(((r % (int64_t)kLweQ) + kLweQ) % kLweQ);
         bits[c] = (uint8_t)((HERDB_PT_MOD * rr) / kLweQ);
     }
-    return HERDB_OK;
+    return 0;
 }
 
 }  // extern "C"

@@ -32,7 +32,7 @@ EXPORTS = [
     "herdb_map_async", "herdb_reduce_async", "herdb_reduce_rows", "herdb_wait_idle", "herdb_partition_read", "herdb_partition_write", "herdb_partition_rows",
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_pipeline_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_circuit_schedule", "herdb_circuit_eval_plain", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
-    "herdb_client_key_blob_size", "herdb_client_keygen", "herdb_client_encrypt_bits", "herdb_client_decrypt_bits",
+    "herdb_task_threads", "herdb_key_blob_size", "herdb_loaded_keys", "herdb_partition_count", "herdb_eval_gate_batch_dev_shape",
 ]
 
 
@@ -47,7 +47,8 @@ class herdb_stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("gates_bootstrapped", C.c_uint64),
                 ("blind_rotate_ms", C.c_double), ("keyswitch_ms", C.c_double),
                 ("blind_rotate_launches", C.c_uint64), ("keyswitch_launches", C.c_uint64),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("key_load_ms", C.c_double), ("key_bcast_ms", C.c_double)]
 
 
 DONE_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int)
@@ -76,8 +77,8 @@ def lib():
         L.herdb_load_key_dev.argtypes = [vp, cp, ci, vp, sz]
         L.herdb_unload_key.argtypes = [vp, cp]
         L.herdb_key_lwe_n.argtypes = [vp, cp, C.POINTER(u32)]
-        L.herdb_map_async.argtypes = [vp, cp, cp, u32, u64, cp, u32, C.POINTER(herdb_circuit), DONE_FN, vp]
-        L.herdb_reduce_async.argtypes = [vp, cp, C.POINTER(herdb_input_frame), sz, cp, u32, C.POINTER(herdb_circuit), DONE_FN, vp]
+        L.herdb_map_async.argtypes = [vp, cp, cp, u32, u64, cp, u32, ci, C.POINTER(herdb_circuit), DONE_FN, vp]
+        L.herdb_reduce_async.argtypes = [vp, cp, C.POINTER(herdb_input_frame), sz, cp, u32, ci, C.POINTER(herdb_circuit), DONE_FN, vp]
         L.herdb_reduce_rows.argtypes = [vp, cp, C.POINTER(herdb_circuit), vp, sz, vp]
         L.herdb_wait_idle.argtypes = [vp]
         L.herdb_partition_read.argtypes = [cp, u64, sz, vp]
@@ -95,10 +96,11 @@ def lib():
         L.herdb_get_stream.argtypes = [vp, ci, C.POINTER(vp)]
         L.herdb_reset_stats.argtypes = [vp]
         L.herdb_measure_int_peak.argtypes = [vp, ci] + [C.POINTER(C.c_double)] * 5
-        L.herdb_client_key_blob_size.argtypes = [u32]; L.herdb_client_key_blob_size.restype = sz
-        L.herdb_client_keygen.argtypes = [u32, u64, vp, vp, vp, sz]
-        L.herdb_client_encrypt_bits.argtypes = [u32, vp, u64, u64, vp, sz, vp]
-        L.herdb_client_decrypt_bits.argtypes = [u32, vp, vp, sz, vp]
+        L.herdb_task_threads.argtypes = [vp]
+        L.herdb_key_blob_size.argtypes = [u32]; L.herdb_key_blob_size.restype = sz
+        L.herdb_loaded_keys.argtypes = [vp]
+        L.herdb_partition_count.argtypes = [cp, sz, C.POINTER(u64)]
+        L.herdb_eval_gate_batch_dev_shape.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz, ci]
         _lib = L
     return _lib
 
@@ -172,34 +174,13 @@ def partition_rows(rows, partitions, k):
     return lib().herdb_partition_rows(rows, partitions, k)
 
 
-# ------------------------------------------------------------------------------------------------ client stand-in
-def client_keygen(n, seed=0x48455244):
-    """synthetic herd-client key generation: (sk_lwe, sk_ring, key blob); host only"""
-    L = lib()
-    sk = np.zeros(n, np.int8); skr = np.zeros(RING_N, np.int8)
-    blob = np.zeros(L.herdb_client_key_blob_size(n), np.uint8)
-    rc = L.herdb_client_keygen(n, seed, _ptr(sk), _ptr(skr), _ptr(blob), blob.size)
+def partition_count(path, bits, n):
+    """rows in a partition file of `bits` ciphertexts per row (reads to the end of the file)"""
+    cnt = C.c_uint64()
+    rc = lib().herdb_partition_count(str(path).encode(), bits * (n + 1) * 2, C.byref(cnt))
     if rc:
-        raise HerdbError(rc)
-    return sk, skr, blob
-
-
-def client_encrypt_bits(n, sk, bits, seed=1, first=0, out=None):
-    bits = np.ascontiguousarray(bits, np.uint8)
-    cts = out if out is not None else np.empty(bits.shape + (n + 1,), np.uint16)
-    rc = lib().herdb_client_encrypt_bits(n, _ptr(sk), seed, first, _ptr(bits), bits.size, _ptr(cts))
-    if rc:
-        raise HerdbError(rc)
-    return cts
-
-
-def client_decrypt_bits(n, sk, cts):
-    cts = np.ascontiguousarray(cts, np.uint16)
-    bits = np.zeros(cts.shape[:-1], np.uint8)
-    rc = lib().herdb_client_decrypt_bits(n, _ptr(sk), _ptr(cts), bits.size, _ptr(bits))
-    if rc:
-        raise HerdbError(rc)
-    return bits
+        raise HerdbError(rc, str(path))
+    return cnt.value
 
 
 # ------------------------------------------------------------------------------------------------ backend
@@ -245,6 +226,12 @@ class Backend:
     def unload_key(self, session):
         self._check(self.L.herdb_unload_key(self.h, session.encode()))
 
+    def loaded_keys(self):
+        return self.L.herdb_loaded_keys(self.h)
+
+    def task_threads(self):
+        return self.L.herdb_task_threads(self.h)
+
     def key_lwe_n(self, session):
         n = C.c_uint32()
         self._check(self.L.herdb_key_lwe_n(self.h, session.encode(), C.byref(n)))
@@ -260,9 +247,13 @@ class Backend:
         self._check(self.L.herdb_eval_gate_batch(self.h, session.encode(), device, g, _ptr(a), _ptr(b), _ptr(out), batch))
         return out
 
-    def eval_gate_batch_dev(self, session, gate, d_a, d_b, d_out, batch, device=0):
+    def eval_gate_batch_dev(self, session, gate, d_a, d_b, d_out, batch, device=0, shape=None):
+        """shape: ciphertexts per CTA forced to 4, 2 or 1 (None / 0 = the launch policy)"""
         g = GATE[gate] if isinstance(gate, str) else int(gate)
-        self._check(self.L.herdb_eval_gate_batch_dev(self.h, session.encode(), device, g, _ptr(d_a), _ptr(d_b), _ptr(d_out), batch))
+        if shape:
+            self._check(self.L.herdb_eval_gate_batch_dev_shape(self.h, session.encode(), device, g, _ptr(d_a), _ptr(d_b), _ptr(d_out), batch, shape))
+        else:
+            self._check(self.L.herdb_eval_gate_batch_dev(self.h, session.encode(), device, g, _ptr(d_a), _ptr(d_b), _ptr(d_out), batch))
 
     def eval_circuit_rows(self, session, circuit: Circuit, rows_in, out=None):
         n = self.key_lwe_n(session)
@@ -404,9 +395,9 @@ class TaskHandle:
 class CudaWorkerGroup:
     """IWorkerGroup (i_worker_group.hpp:44-48) backed by the in-process CUDA backend."""
 
-    def __init__(self, storage_dir, key_dir, devices=(0,), concurrent=2):
+    def __init__(self, storage_dir, key_dir, devices=(0,)):
         self.backend = Backend(devices, storage_dir, key_dir)
-        self._concurrent = concurrent
+        self._concurrent = self.backend.task_threads()      # tasks the backend really runs at once
         self._handles = {}
         self._next = 1
         self._lock = threading.Lock()
@@ -435,7 +426,7 @@ class CudaWorkerGroup:
                 frames[k] = herdb_input_frame(f.pointer.uuid.encode(), f.pointer.partition, f.row_count)
             rc = B.L.herdb_reduce_async(B.h, task.session_uuid.encode(), frames, len(task.input_data_frame_ptrs),
                                         task.output_data_frame_ptr.uuid.encode(), task.output_data_frame_ptr.partition,
-                                        C.byref(cc), self._done, tag)
+                                        int(task.crypto_key_ptr.schema_type), C.byref(cc), self._done, tag)
             if rc:
                 with self._lock:
                     self._handles.pop(tag, None)
@@ -445,7 +436,7 @@ class CudaWorkerGroup:
                                  task.input_data_frame_ptr.pointer.uuid.encode(), task.input_data_frame_ptr.pointer.partition,
                                  task.input_data_frame_ptr.row_count,
                                  task.output_data_frame_ptr.uuid.encode(), task.output_data_frame_ptr.partition,
-                                 C.byref(cc), self._done, tag)
+                                 int(task.crypto_key_ptr.schema_type), C.byref(cc), self._done, tag)
         if rc:
             with self._lock:
                 self._handles.pop(tag, None)

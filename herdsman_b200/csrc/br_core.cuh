@@ -28,9 +28,15 @@
 
 namespace herdb {
 
-// ciphertexts per CTA is a template parameter C (2 or 4); a CTA has 64*C threads = 2*C warps, one
-// warp per (ciphertext, component) polynomial in phase A, 16/C evaluation points per thread in phase B
+// Ciphertexts per CTA is a template parameter C.  C = 4 is the throughput shape: 256 threads = 8 warps, one warp
+// per (ciphertext, component) polynomial in phase A, 4 evaluation points per thread in phase B, key rows 2..7
+// staged by cp.async into slots freed inside the MAC loop.  C = 2 and C = 1 are the small-job shapes (launches
+// and launch tails that would leave SMs empty at C = 4): 128 threads, 8 evaluation points per thread in phase
+// B; with fewer ciphertexts there is room for the whole 128 KiB key slice of a step, so all eight rows arrive
+// by TMA bulk copies at step start and phase B has no staging at all.  At C = 1 only warps 0 and 1 have a
+// polynomial in phase A; all four warps share phase B.
 constexpr int kCMax = 4;
+template <int C> struct BrShape { static constexpr u32 kThreads = C == 4 ? 256u : 128u; };
 constexpr u32 kExtStride = 1032;            // u16 words per extracted ciphertext (N + 1, padded to 16 B)
 constexpr u32 kLweMax = HERDB_N_STD128;     // largest LWE dimension supported by the smem layout
 
@@ -44,7 +50,10 @@ struct GateDesc {
     uint8_t pad[2];
     u32 idx_a, idx_b, idx_out;   // ciphertext index inside a row of the pool
 };
-struct Pool { u16* base; u32 row_cts; u32 pad; };    // ciphertext (r, idx) at base + (r*row_cts + idx)*(n+1)
+// ciphertext (row r, idx) of a pool at base + r*row_words + idx*(n+1).  Dense rows: row_words = cts_per_row*(n+1).
+// Rows in herdsman's partition framing ([u32 length][payload], storage_service.cpp:19-28) are used in place:
+// row_words = 2 + cts_per_row*(n+1) and base points behind the first length word.
+struct Pool { u16* base; u32 row_words; u32 pad; };
 
 struct BrParams {
     const u32* bsk;              // [n][2 sign][8 rows][2 cols][1024]  NTT domain, canonical, rows folded by fold_top_digit, words at key_pos
@@ -59,6 +68,8 @@ struct BrParams {
     u32 steps;                   // CMUX steps to run (== n except in debug traces)
     u32 rows;                    // rows in this chunk
     u32 jobs;                    // gates_in_level * rows;  job -> gate = job / rows, row = job % rows
+    u32 job0, job1;              // this launch covers jobs [job0, job1): a level may be cut into a body of whole grid
+                                 // rounds at C = 4 and a tail at a smaller shape
 };
 
 template <int C>
@@ -67,7 +78,8 @@ struct BrSmem {
     u32 dig[C][2 * kDGT][kN];
     u32 itw[kLaneTwWords];       // inverse pass-1 lane twiddles
     u32 ftw[kLaneTwWords];       // forward pass-2 lane twiddles (streamed by fwd_pass2_stream)
-    u32 kst[2][4][kN];           // bootstrapping-key staging ring (cp.async): two digits x (sign, column) x 1024 points
+    u32 kst[C == 4 ? 2 : 8][4][kN];   // C = 4: bootstrapping-key staging ring (cp.async), two rows x (sign, column) x 1024 points;
+                                 // C < 4: the whole key slice of a step, eight rows (bulk copies)
     u32 mono[C][2][kN];          // the two monomial rows of this step per ciphertext (cp.async, land during phase A)
     u16 lwe[C][kLweMax + 8];
     u32 gate_b[C];               // prepared b and gate code per ciphertext
@@ -87,7 +99,7 @@ HERDB_HD u32 gate_const_eighths(u32 gate) {
 // one LWE word of an operand after the free transforms (EvalNOT / trivial constant)
 HERDB_HD u32 operand_word(const Pool* pools, u32 pool, u32 idx, u32 flags, u32 row, u32 n, u32 k) {
     if (flags & kOpConst) return k == n ? ((flags & kOpConstVal) ? kLweQ / HERDB_PT_MOD : 0u) : 0u;
-    u32 v = pools[pool].base[((size_t)row * pools[pool].row_cts + idx) * (n + 1) + k];
+    u32 v = pools[pool].base[(size_t)row * pools[pool].row_words + (size_t)idx * (n + 1) + k];
     if (flags & kOpNeg) v = (k == n) ? ((kLweQ >> 2) + kLweQ - v) & (kLweQ - 1) : (kLweQ - v) & (kLweQ - 1);
     return v;
 }
@@ -97,15 +109,19 @@ template <int kC, class Env>
 // `bar_phase0`: parity of the number of bulk-copy phases S.bar has completed before this group (the caller
 // initialises S.bar once, with one expected arrival, and runs groups back to back: steps of earlier groups)
 HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32 group, u32 bar_phase0) {
-    constexpr u32 kThreads = 64 * kC;
-    static_assert(kC == 4, "the key staging scheme recycles four digit slots for the four (sign, column) pieces");
+    constexpr u32 kThreads = BrShape<kC>::kThreads;
+    constexpr int kChunks = (int)(kN / 4 / kThreads);              // chunks of 4 evaluation points per thread in phase B
+    constexpr bool kRing = kC == 4;                                // key rows 2..7 through the cp.async ring (else: all rows by bulk copy)
+    static_assert(kC == 4 || kC == 2 || kC == 1, "CTA shapes: 4 (throughput), 2 and 1 (small launches and tails)");
+    static_assert(!kRing || kChunks == 1, "the ring recycles the four digit slots of four ciphertexts for the four (sign, column) pieces");
     const u32 tid = env.tid();
     const u32 lane = tid & 31, warp = tid >> 5;
+    const bool has_poly = warp < 2u * kC;                          // phase A: warp = (ciphertext, component)
     const u32 n = P.n;
 
     // ---- ciphertext preparation: ct1 + ct2 (2*(ct1 - ct2) for XOR_FAST / XNOR_FAST), NOT folded in
     for (int c = 0; c < kC; ++c) {
-        u32 job = group * kC + c; if (job >= P.jobs) job = P.jobs - 1;
+        u32 job = P.job0 + group * kC + c; if (job >= P.job1) job = P.job1 - 1;
         const GateDesc g = P.gates[job / P.rows];
         const u32 row = job % P.rows;
         for (u32 k = tid; k <= n; k += kThreads) {
@@ -124,7 +140,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 #endif
     env.sync();
     // ---- BootstrapGateCore: acc = (0, NTT(m)), m[2j] = +-(Q/8+1) depending on (b - j) in [q1, q2)
-    {
+    if (has_poly) {
         const int c = warp >> 1, j = warp & 1;
         u32 x[32];
         if (j == 0) {
@@ -156,31 +172,25 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
 
     // ---- EvalAcc: n CMUX steps (AddToAccCGGI)
     for (u32 i = 0; i < P.steps; ++i) {
-        // Key slice of this step.  Rows 0 and 1 and the eight monomial rows X^(+-a_i) - 1 (64 KiB, sixteen 4 KiB
+        // Key slice of this step.  C = 4: rows 0 and 1 and the eight monomial rows X^(+-a_i) - 1 (64 KiB, sixteen 4 KiB
         // pieces) are fetched by TMA bulk copies that ONE thread issues right after the barrier that ended the
         // previous step (every thread has finished reading the destinations); they land during phase A and are
         // awaited on an mbarrier at the start of phase B.  Rows 2..7 cannot be fetched that way: their
         // destinations are slots a thread frees in the middle of the MAC loop, so each thread copies exactly the
         // 16-byte pieces it will itself consume with cp.async (completion = cp.async.wait_group, no barrier):
         // into the ring stage and the digit slots it has already read.
-        const u32* K = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN) + 4 * tid;
-        const u32 phys_b = swz(4 * tid);
-        const u32 lin_b = 4 * tid;                                       // staging ring and monomials are stored linearly
-        auto stage_key = [&](int r, u32* dst0, u32 dst_stride) {      // piece (s, jo) of digit r -> dst0 + (2*s + jo)*dst_stride
-#pragma unroll
-            for (int s = 0; s < 2; ++s)
-#pragma unroll
-                for (int jo = 0; jo < 2; ++jo) env.cp16(dst0 + (2 * s + jo) * dst_stride, K + ((s * kDG2 + r) * 2 + jo) * kN);
-        };
+        // C < 4: shared memory holds the whole slice, all eight rows come by bulk copy and nothing is recycled.
+        const u32* Kstep = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN);
+        constexpr u32 kDigCt = 2 * kDGT * kN;           // words between the digit blocks of two ciphertexts
         if (tid == 0) {
-            const u32* Kb = P.bsk + (size_t)i * (2 * kDG2 * 2 * kN);
-            env.bulk_begin(&S.bar, (2 * 4 + 2 * kC) * kN * 4);
+            constexpr int kBulkRows = kRing ? 2 : (int)kDG2;
+            env.bulk_begin(&S.bar, (kBulkRows * 4 + 2 * kC) * kN * 4);
 #pragma unroll
-            for (int r = 0; r < 2; ++r)
+            for (int r = 0; r < kBulkRows; ++r)
 #pragma unroll
                 for (int s = 0; s < 2; ++s)
 #pragma unroll
-                    for (int jo = 0; jo < 2; ++jo) env.bulk_copy(&S.kst[r][2 * s + jo][0], Kb + ((s * kDG2 + r) * 2 + jo) * kN, kN * 4, &S.bar);
+                    for (int jo = 0; jo < 2; ++jo) env.bulk_copy(&S.kst[r][2 * s + jo][0], Kstep + ((s * kDG2 + r) * 2 + jo) * kN, kN * 4, &S.bar);
 #pragma unroll
             for (int cc = 0; cc < kC; ++cc) {
                 const u32 a = S.lwe[cc][i];
@@ -191,7 +201,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
             }
         }
         // ===== phase A: warp = (ciphertext c, component j)
-        {
+        if (has_poly) {
             const int c = warp >> 1, j = warp & 1;
             u32 x[32];
             load_contig(S.acc[c][j], lane, x);
@@ -230,10 +240,20 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
         }
         env.sync();
         // ===== phase B: thread = kChunks chunks of 4 evaluation points: 4*(tid + q*kThreads) ..+3
-        {
+#pragma unroll 1
+        for (int q = 0; q < kChunks; ++q) {
             // exactness of the 64-bit sums: six digit transforms below kFwdOutMax and the two accumulator components
             // below 2Q, each times a key word below Q, stay below 2^62 (what fold62_f64 accepts)
             static_assert((6 * kFwdOutMax + 2 * 2ull * kQ) < ((1ull << 62) / kQ), "key MAC fits 62 bits");
+            const u32 lin_b = 4 * (tid + (u32)q * kThreads);                 // staging ring and monomials are stored linearly
+            const u32 phys_b = swz(lin_b);
+            const u32* K = Kstep + lin_b;
+            auto stage_key = [&](int r, u32* dst0, u32 dst_stride) {      // piece (s, jo) of row r -> dst0 + (2*s + jo)*dst_stride
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+#pragma unroll
+                    for (int jo = 0; jo < 2; ++jo) env.cp16(dst0 + (2 * s + jo) * dst_stride, K + ((s * kDG2 + r) * 2 + jo) * kN);
+            };
             u64 mac[kC][2][2][4];
 #pragma unroll
             for (int c = 0; c < kC; ++c)
@@ -245,17 +265,17 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                         for (int p = 0; p < 4; ++p) mac[c][s][jo][p] = 0;
             // Row r = j + 2l of the key multiplies the transform of digit l of component j for l < 3 and, for
             // l = 3 (r = 6, 7), the stored accumulator component j itself (folded rows, modarith.cuh).
-            // where row r's key pieces live: r = 0,2,6 ring 0; r = 1,4 ring 1; r = 3,5,7 the consumed digit slots 0,1,2
+            // Ring (C = 4), where row r's key pieces live: r = 0,2,6 ring 0; r = 1,4 ring 1; r = 3,5,7 the consumed digit slots 0,1,2
 #pragma unroll
             for (int r = 0; r < (int)kDG2; ++r) {
-                if (r == 0) env.mbar_wait(&S.bar, (bar_phase0 + i) & 1);                      // rows 0, 1 and the monomials (bulk copies)
-                if (r == 2 || r == 4) env.cp_wait1();                          // cp.async groups: {2,3} | {4,5} | {6,7}
-                if (r == 6) env.cp_wait0();
-                const u32* kbase = (r == 0 || r == 2 || r == 6) ? &S.kst[0][0][lin_b]
-                                 : (r == 1 || r == 4)           ? &S.kst[1][0][lin_b]
-                                                                : &S.dig[0][(r - 3) / 2][phys_b];
-                constexpr u32 kDigCt = 2 * kDGT * kN;           // words between the digit blocks of two ciphertexts
-                const u32 kstride = (r == 3 || r == 5 || r == 7) ? kDigCt : kN;
+                if (r == 0 && q == 0) env.mbar_wait(&S.bar, (bar_phase0 + i) & 1);            // the bulk copies of this step
+                if (kRing && (r == 2 || r == 4)) env.cp_wait1();               // cp.async groups: {2,3} | {4,5} | {6,7}
+                if (kRing && r == 6) env.cp_wait0();
+                const u32* kbase = !kRing                          ? &S.kst[r % (kRing ? 2 : 8)][0][lin_b]
+                                 : (r == 0 || r == 2 || r == 6)    ? &S.kst[0][0][lin_b]
+                                 : (r == 1 || r == 4)              ? &S.kst[1][0][lin_b]
+                                                                   : &S.dig[0][(r - 3) / 2][phys_b];
+                const u32 kstride = (kRing && (r == 3 || r == 5 || r == 7)) ? kDigCt : kN;
                 V4 kv[2][2];
 #pragma unroll
                 for (int s = 0; s < 2; ++s)
@@ -275,7 +295,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                 }
                 // digit r is consumed: its slots (and the ring stage it came from) take the next pieces.  The
                 // asm operands make the copies wait for this iteration's shared-memory reads (dep, kv).
-                if (r <= 2) {
+                if (kRing && r <= 2) {
                     env.cp_fence(dep ^ kv[1][1].v[0]);
                     stage_key(2 * r + 2, &S.kst[r & 1][0][lin_b], kN);
                     stage_key(2 * r + 3, &S.dig[0][r][phys_b], kDigCt);
@@ -304,9 +324,9 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
     }
 
     // ---- back to coefficients, Transpose(acc[0]) -> LWE a, acc[1][0] + Q/8 + 1 -> b, ModSwitch(qKS)
-    {
+    if (has_poly) {
         const int c = warp >> 1, j = warp & 1;
-        const u32 job = group * kC + c;
+        const u32 job = P.job0 + group * kC + c;
         u32 x[32];
         load_contig(S.acc[c][j], lane, x);
         inv_pass1<1, 2>(x, S.itw, lane);
@@ -314,7 +334,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
         env.syncwarp();
         load_strided(S.dig[c][j], lane, x);
         inv_pass2<2, 1>(x);
-        if (job < P.jobs) {
+        if (job < P.job1) {
             u16* ext = P.ext + (size_t)job * kExtStride;
 #pragma unroll
             for (int k = 0; k < 32; ++k) {

@@ -22,11 +22,6 @@ struct DevEnv {
     __device__ __forceinline__ u32 tid() const { return threadIdx.x; }
     __device__ __forceinline__ void sync() { __syncthreads(); }
     __device__ __forceinline__ void syncwarp() { __syncwarp(); }
-    __device__ __forceinline__ V4 ldg_v4(const u32* p) const {
-        uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
-        V4 r; r.v[0] = q.x; r.v[1] = q.y; r.v[2] = q.z; r.v[3] = q.w;
-        return r;
-    }
     // 16-byte asynchronous global -> shared copy (LDGSTS, L2 only), grouped by commit / wait_group
     __device__ __forceinline__ void cp16(u32* smem_dst, const u32* gsrc) const {
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((u32)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
@@ -34,7 +29,6 @@ struct DevEnv {
     __device__ __forceinline__ void cp_commit() const { asm volatile("cp.async.commit_group;" ::: "memory"); }
     __device__ __forceinline__ void cp_wait1() const { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
     __device__ __forceinline__ void cp_wait0() const { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-    __device__ __forceinline__ void delay(u32 clocks) const { const long long t0 = clock64(); while (clock64() - t0 < (long long)clocks) { } }
     // TMA bulk copies (cp.async.bulk, global -> shared) completing on an mbarrier
     __device__ __forceinline__ void mbar_init(unsigned long long* bar, u32 count) const {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((u32)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
@@ -55,13 +49,13 @@ struct DevEnv {
     __device__ __forceinline__ void cp_fence(u32 dep) const { asm volatile("" ::"r"(dep) : "memory"); }
 };
 
-// persistent over groups of C = 4 jobs: one 256-thread CTA per SM (212 KB of shared memory)
+// persistent over groups of C jobs: one CTA per SM (C = 4: 256 threads, 212 KB of shared memory; C = 2, 1: 128 threads)
 template <int C>
-__global__ void __launch_bounds__(64 * C, 1) blind_rotate_kernel(const __grid_constant__ BrParams P) {
+__global__ void __launch_bounds__(BrShape<C>::kThreads, 1) blind_rotate_kernel(const __grid_constant__ BrParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BrSmem<C>& S = *reinterpret_cast<BrSmem<C>*>(smem_raw);
     DevEnv env;
-    const u32 groups = (P.jobs + C - 1) / C;
+    const u32 groups = (P.job1 - P.job0 + C - 1) / C;
     if (threadIdx.x == 0) env.mbar_init(&S.bar, 1);
     __syncthreads();
     u32 done = 0;                                                    // bulk-copy phases completed so far = steps of earlier groups
@@ -105,7 +99,7 @@ __global__ void __launch_bounds__(kKsThreads) keyswitch_kernel(const __grid_cons
             }
             const GateDesc g = P.gates[job / P.rows];
             const u32 row = job % P.rows;
-            u16* out = P.pools[g.pool_out].base + ((size_t)row * P.pools[g.pool_out].row_cts + g.idx_out) * (P.n + 1);
+            u16* out = P.pools[g.pool_out].base + (size_t)row * P.pools[g.pool_out].row_words + (size_t)g.idx_out * (P.n + 1);
             const u32 sums[4] = {acc0 & 0xFFFFu, acc0 >> 16, acc1 & 0xFFFFu, acc1 >> 16};
 #pragma unroll
             for (u32 e = 0; e < 4; ++e) {
@@ -119,17 +113,26 @@ __global__ void __launch_bounds__(kKsThreads) keyswitch_kernel(const __grid_cons
     }
 }
 
-// OutputNode: rows_out[row][o] = operand (with NOT / constant folding applied)
+// OutputNode: output row[o] = operand (with NOT / constant folding applied).  The output pool may be in the
+// partition framing: frame_len != 0 also writes the u32 length word in front of every row, so that the buffer
+// is the byte image of the partition file (storage_service.cpp:19-28) and the host writes it out unchanged.
 __global__ void gather_outputs_kernel(const __grid_constant__ GatherParams P) {
     const u32 w = P.n + 1;
+    const Pool out = P.pools[kGatherOutPool];
     const size_t total = (size_t)P.rows * P.out_bits * w;
     for (size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (size_t)gridDim.x * blockDim.x) {
         const u32 k = (u32)(t % w);
         const size_t ct = t / w;
         const u32 o = (u32)(ct % P.out_bits), row = (u32)(ct / P.out_bits);
         const OutDesc d = P.outs[o];
-        P.rows_out[t] = (u16)operand_word(P.pools, d.pool, d.idx, d.flags, row, P.n, k);
+        u16* dst = out.base + (size_t)row * out.row_words;
+        dst[(size_t)o * w + k] = (u16)operand_word(P.pools, d.pool, d.idx, d.flags, row, P.n, k);
+        if (P.framed && o == 0 && k < 2) dst[(int)k - 2] = (u16)(P.frame_len >> (16 * k));     // little-endian host (x86-64 / aarch64)
     }
+    if (P.framed && !P.out_bits)                                  // rows without payload still carry their length word
+        for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < P.rows; r += (size_t)gridDim.x * blockDim.x) {
+            u16* dst = out.base + r * out.row_words; dst[-2] = 0; dst[-1] = 0;
+        }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -228,19 +231,42 @@ __global__ void __launch_bounds__(256) int_peak_kernel(u32* out, u32 seed, int i
 // ------------------------------------------------------------------------------------------------
 // launchers (plain C++ signatures so backend.cpp does not need nvcc)
 template <int C>
-static cudaError_t launch_br(const BrParams& P, int sm_count, cudaStream_t stream) {
+static cudaError_t launch_br(BrParams P, u32 job0, u32 job1, int sm_count, cudaStream_t stream) {
+    if (job1 <= job0) return cudaSuccess;
     // per device attribute; cheap enough to set on every launch (launches last milliseconds)
     cudaError_t e = cudaFuncSetAttribute(blind_rotate_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BrSmem<C>));
     if (e != cudaSuccess) return e;
-    const u32 groups = (P.jobs + C - 1) / C;
-    if (!groups) return cudaSuccess;
+    P.job0 = job0; P.job1 = job1;
+    const u32 groups = (job1 - job0 + C - 1) / C;
     const u32 resident = (u32)sm_count;
     const u32 grid = groups < resident ? groups : resident;
-    blind_rotate_kernel<C><<<grid, 64 * C, sizeof(BrSmem<C>), stream>>>(P);
+    blind_rotate_kernel<C><<<grid, BrShape<C>::kThreads, sizeof(BrSmem<C>), stream>>>(P);
     return cudaGetLastError();
 }
-cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream) {
-    return launch_br<4>(P, sm_count, stream);
+// A level of P.jobs jobs = a body of whole grid rounds at C = 4 (one CTA per SM, four ciphertexts each) and a tail.
+// A tail that would fill at most half (a quarter) of the SMs at C = 4 runs as its own launch at C = 2 (C = 1): twice
+// (four times) the SMs, each with a shorter step.  `shape` forces one CTA shape (0 = this policy); launches_out
+// (may be null) receives the number of kernels launched.
+cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream, int shape, int* launches_out) {
+    const u32 sm = (u32)sm_count, jobs = P.jobs;
+    int launches = 0;
+    cudaError_t e = cudaSuccess;
+    if (shape == 4 || shape == 2 || shape == 1) {
+        e = shape == 4 ? launch_br<4>(P, 0, jobs, sm_count, stream) : shape == 2 ? launch_br<2>(P, 0, jobs, sm_count, stream) : launch_br<1>(P, 0, jobs, sm_count, stream);
+        launches = jobs ? 1 : 0;
+    } else {
+        const u32 wave = 4 * sm;
+        u32 body = jobs / wave * wave;
+        const u32 tail = jobs - body;
+        if (tail > 2 * sm) body = jobs;                                  // the tail is worth a C = 4 round of its own
+        if (body) { e = launch_br<4>(P, 0, body, sm_count, stream); ++launches; }
+        if (e == cudaSuccess && body < jobs) {
+            e = tail > sm ? launch_br<2>(P, body, jobs, sm_count, stream) : launch_br<1>(P, body, jobs, sm_count, stream);
+            ++launches;
+        }
+    }
+    if (launches_out) *launches_out = launches;
+    return e;
 }
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream) {
     if (!P.jobs) return cudaSuccess;
@@ -251,7 +277,7 @@ cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t strea
     return cudaGetLastError();
 }
 cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream) {
-    if (!P.rows || !P.out_bits) return cudaSuccess;
+    if (!P.rows || (!P.out_bits && !P.framed)) return cudaSuccess;
     gather_outputs_kernel<<<sm_count * 8, 256, 0, stream>>>(P);
     return cudaGetLastError();
 }

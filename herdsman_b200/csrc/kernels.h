@@ -14,14 +14,16 @@ struct KsParams {
     u32 n, rows, jobs;
 };
 struct OutDesc { u32 idx; uint8_t pool, flags, pad[2]; };
+constexpr u32 kGatherOutPool = 3;   // == kPoolOut (circuit.h)
 struct GatherParams {
     const OutDesc* outs;         // [out_bits]
-    Pool pools[4];
-    u16* rows_out;               // [rows][out_bits][n+1]
+    Pool pools[4];               // pools[kGatherOutPool] = the output rows
     u32 n, rows, out_bits;
+    u32 framed;                  // != 0: output rows are in the partition framing: write the u32 length word before every row
+    u32 frame_len;               // that length (payload bytes of an output row)
 };
 
-cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream);
+cudaError_t launch_blind_rotate(const BrParams& P, int sm_count, cudaStream_t stream, int shape = 0, int* launches_out = nullptr);
 cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t stream);
 cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream);
 cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 polys, int sm_count, cudaStream_t stream);

@@ -10,20 +10,30 @@
 // It depends only on herdsman's own headers and on herdb.h / libherdb.so.  It is header-only so
 // that herdsman's CMake needs one include directory and one link line.
 //
-// Completion contract: schedule_task returns a PENDING handle; the backend's host
-// thread fires mark_completed() after the output partition file is in place.  The executor
-// installs its callback after schedule_task returns (src/execution/executor/executor.cpp:86-93);
-// TaskHandle::set_completion_callback is not virtual, so -- exactly like GrpcWorkerGroup -- a task
-// that completes before the callback is installed would be lost.  The backend therefore never
-// completes a task from inside schedule_task, and completion of real tasks takes milliseconds at
-// least; for the malformed-task case (refused synchronously) completion is deferred to a detached
-// thread that waits for the callback to be installed.
+// Completion contract: schedule_task returns a PENDING handle; a backend host thread completes
+// it after the output partition file is in place.  The executor installs its callback only AFTER
+// schedule_task has returned (src/execution/executor/executor.cpp:86-93) and
+// TaskHandle::set_completion_callback is neither virtual nor re-firing (i_worker_group.cpp:4-20), so a
+// completion that arrives in between would be dropped and the job would hang.  A task can fail within
+// microseconds (missing key file, missing partition, refused circuit), so this is a real window, not a
+// theoretical one.  The adapter closes it without touching herdsman:
+//   * schedule_task is only ever called from the single executor thread (executor.cpp:46-80), and that thread
+//     calls concurrent_workers() right after every schedule_task_on_worker (the loop condition of
+//     schedule_tasks_on_workers, executor.cpp:96-113).  So whenever the executor thread ENTERS schedule_task
+//     or concurrent_workers, the callback of every handle returned earlier is installed: those handles are
+//     "armed".
+//   * A completion of an armed handle fires at once on the backend thread.  A completion of a handle that is
+//     not armed yet is parked; the executor thread's next entry (at most the time of one
+//     set_completion_callback away) releases it, and a completer thread releases parked completions after a
+//     bounded wait (kArmTimeout) for callers that never come back.
 #ifndef HERD_B200_CUDA_WORKER_GROUP_HPP
 #define HERD_B200_CUDA_WORKER_GROUP_HPP
 
 #include <atomic>
 #include <cassert>
 #include <chrono>
+#include <condition_variable>
+#include <deque>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -46,12 +56,13 @@ public:
 		[[nodiscard]] Status status() const noexcept override { return status_.load(); }
 		void complete(Status status) { status_.store(status); mark_completed(); }
 	private:
+		friend class CudaWorkerGroup;
 		std::atomic<Status> status_{Status::PENDING};
+		uint64_t epoch_ = 0;                                             // value of group.next_epoch_ when the handle was returned
 	};
 
 	CudaWorkerGroup(const std::vector<int>& devices, const std::string& storage_directory,
-	                const std::string& key_directory, std::size_t concurrent_tasks = 2)
-		: concurrent_(concurrent_tasks)
+	                const std::string& key_directory)
 	{
 		const int rc = herdb_create(&ctx_, devices.data(), static_cast<int>(devices.size()),
 		                            storage_directory.c_str(), key_directory.c_str());
@@ -59,24 +70,45 @@ public:
 		{
 			throw std::runtime_error(std::string("CudaWorkerGroup: ") + herdb_strerror(rc));
 		}
+		concurrent_ = static_cast<std::size_t>(herdb_task_threads(ctx_));   // tasks the backend really runs at once
+		completer_ = std::thread([this]() { completer_body(); });
 	}
 
-	~CudaWorkerGroup() override { herdb_destroy(ctx_); }
+	~CudaWorkerGroup() override
+	{
+		herdb_destroy(ctx_);                                             // waits for running tasks; their completions are parked or fired
+		{
+			std::unique_lock lock(arm_mutex_);
+			shutting_down_ = true;
+		}
+		arm_cv_.notify_all();
+		completer_.join();
+	}
 
 	CudaWorkerGroup(const CudaWorkerGroup&) = delete;
 	CudaWorkerGroup& operator=(const CudaWorkerGroup&) = delete;
 
-	std::size_t concurrent_workers() const noexcept override { return concurrent_; }
+	std::size_t concurrent_workers() const noexcept override
+	{
+		const_cast<CudaWorkerGroup*>(this)->arm_returned_handles();      // executor thread: everything returned so far has its callback
+		return concurrent_;
+	}
 
 	std::shared_ptr<TaskHandle> schedule_task(const herd::common::task_t& task) override
 	{
 		assert(!std::holds_alternative<std::monostate>(task));          // grpc_worker_group.cpp:74
+		arm_returned_handles();
 		auto handle = std::make_shared<CudaTaskHandle>();
+		{
+			std::unique_lock lock(arm_mutex_);
+			handle->epoch_ = next_epoch_++;
+		}
 		auto* pending = new Pending{this, handle};
 		{
 			std::unique_lock lock(pending_mutex_);
 			pending_[pending] = handle;                                  // keeps the handle alive (grpc_worker_group.cpp:100)
 		}
+		int rc = HERDB_OK;
 		if(std::holds_alternative<herd::common::ReduceTask>(task))       // task.hpp:23-32
 		{
 			const auto& reduce_task = std::get<herd::common::ReduceTask>(task);
@@ -89,27 +121,28 @@ public:
 				uuids.emplace_back(ptr.pointer.uuid.as_string());
 				frames.push_back(herdb_input_frame{uuids.back().c_str(), ptr.pointer.partition, ptr.row_count});
 			}
-			const int rc = herdb_reduce_async(
+			rc = herdb_reduce_async(
 					ctx_, reduce_task.session_uuid.as_string().c_str(), frames.data(), frames.size(),
 					reduce_task.output_data_frame_ptr.uuid.as_string().c_str(), reduce_task.output_data_frame_ptr.partition,
+					static_cast<int>(reduce_task.crypto_key_ptr.schema_type),          // key file = <int(SchemaType)>.key, key_service.cpp:28-31
 					&flat.circuit, &CudaWorkerGroup::on_done, pending);
-			if(rc != HERDB_OK)
-			{
-				refuse(pending, handle);
-			}
-			return handle;
 		}
-		const auto& map_task = std::get<herd::common::MapTask>(task);
-		Flat flat = flatten(map_task.circuit);
-		const int rc = herdb_map_async(
-				ctx_, map_task.session_uuid.as_string().c_str(),
-				map_task.input_data_frame_ptr.pointer.uuid.as_string().c_str(), map_task.input_data_frame_ptr.pointer.partition,
-				map_task.input_data_frame_ptr.row_count,
-				map_task.output_data_frame_ptr.uuid.as_string().c_str(), map_task.output_data_frame_ptr.partition,
-				&flat.circuit, &CudaWorkerGroup::on_done, pending);
+		else
+		{
+			const auto& map_task = std::get<herd::common::MapTask>(task);
+			Flat flat = flatten(map_task.circuit);
+			rc = herdb_map_async(
+					ctx_, map_task.session_uuid.as_string().c_str(),
+					map_task.input_data_frame_ptr.pointer.uuid.as_string().c_str(), map_task.input_data_frame_ptr.pointer.partition,
+					map_task.input_data_frame_ptr.row_count,
+					map_task.output_data_frame_ptr.uuid.as_string().c_str(), map_task.output_data_frame_ptr.partition,
+					static_cast<int>(map_task.crypto_key_ptr.schema_type),
+					&flat.circuit, &CudaWorkerGroup::on_done, pending);
+		}
 		if(rc != HERDB_OK)
 		{
-			refuse(pending, handle);
+			// refused synchronously (malformed circuit, ...): ERROR, delivered like any other completion
+			on_done(pending, HERDB_TASK_ERROR);
 		}
 		return handle;
 	}
@@ -117,16 +150,6 @@ public:
 private:
 	struct Pending { CudaWorkerGroup* group; std::shared_ptr<CudaTaskHandle> handle; };
 
-	// the backend refused the task synchronously (malformed circuit, ...): ERROR, but not from inside schedule_task
-	void refuse(Pending* pending, const std::shared_ptr<CudaTaskHandle>& handle)
-	{
-		{
-			std::unique_lock lock(pending_mutex_);
-			pending_.erase(pending);
-		}
-		delete pending;
-		fail_later(handle);
-	}
 	struct Flat
 	{
 		std::vector<herdb_node> nodes;
@@ -188,33 +211,93 @@ private:
 		return flat;
 	}
 
+	static constexpr std::chrono::milliseconds kArmTimeout{200};
+
+	// called on the executor thread: handles returned before this point have their callback installed
+	void arm_returned_handles()
+	{
+		std::deque<Parked> release;
+		{
+			std::unique_lock lock(arm_mutex_);
+			armed_epoch_ = next_epoch_;
+			release.swap(parked_);
+		}
+		for(auto& parked: release)
+		{
+			parked.handle->complete(parked.status);
+		}
+	}
+
+	// backend thread (or schedule_task itself for a refused task): the task is finished
 	static void on_done(void* user, int task_status)
 	{
 		auto* pending = static_cast<Pending*>(user);
+		CudaWorkerGroup* group = pending->group;
+		auto handle = pending->handle;
 		{
-			std::unique_lock lock(pending->group->pending_mutex_);
-			pending->group->pending_.erase(pending);
+			std::unique_lock lock(group->pending_mutex_);
+			group->pending_.erase(pending);
 		}
-		using Status = TaskHandle::Status;
-		pending->handle->complete(task_status == HERDB_TASK_COMPLETED ? Status::COMPLETED
-		                        : task_status == HERDB_TASK_TIME_OUT ? Status::TIME_OUT : Status::ERROR);
 		delete pending;
+		using Status = TaskHandle::Status;
+		const Status status = task_status == HERDB_TASK_COMPLETED ? Status::COMPLETED
+		                    : task_status == HERDB_TASK_TIME_OUT ? Status::TIME_OUT : Status::ERROR;
+		{
+			std::unique_lock lock(group->arm_mutex_);
+			if(handle->epoch_ >= group->armed_epoch_)                      // callback possibly not installed yet: park
+			{
+				group->parked_.push_back(Parked{handle, status, std::chrono::steady_clock::now() + kArmTimeout});
+				lock.unlock();
+				group->arm_cv_.notify_all();
+				return;
+			}
+		}
+		handle->complete(status);
 	}
 
-	// a task refused synchronously must still complete asynchronously (see the header comment)
-	static void fail_later(std::shared_ptr<CudaTaskHandle> handle)
+	// releases parked completions whose bounded wait is over (a caller that never re-enters the group)
+	void completer_body()
 	{
-		std::thread([handle = std::move(handle)]()
+		std::unique_lock lock(arm_mutex_);
+		while(true)
 		{
-			std::this_thread::sleep_for(std::chrono::milliseconds(50));
-			handle->complete(TaskHandle::Status::ERROR);
-		}).detach();
+			if(parked_.empty())
+			{
+				if(shutting_down_) return;
+				arm_cv_.wait(lock);
+				continue;
+			}
+			const auto deadline = parked_.front().deadline;
+			if(!shutting_down_ && std::chrono::steady_clock::now() < deadline)
+			{
+				arm_cv_.wait_until(lock, deadline);
+				continue;
+			}
+			Parked parked = std::move(parked_.front());
+			parked_.pop_front();
+			lock.unlock();
+			parked.handle->complete(parked.status);
+			lock.lock();
+		}
 	}
+
+	struct Parked
+	{
+		std::shared_ptr<CudaTaskHandle> handle;
+		TaskHandle::Status status;
+		std::chrono::steady_clock::time_point deadline;
+	};
 
 	herdb_ctx* ctx_ = nullptr;
-	std::size_t concurrent_;
+	std::size_t concurrent_ = 1;
 	std::mutex pending_mutex_;
 	std::map<Pending*, std::shared_ptr<CudaTaskHandle>> pending_;
+	std::mutex arm_mutex_;
+	std::condition_variable arm_cv_;
+	uint64_t next_epoch_ = 0, armed_epoch_ = 0;                          // handles with epoch < armed_epoch_ have their callback
+	std::deque<Parked> parked_;
+	bool shutting_down_ = false;
+	std::thread completer_;
 };
 
 #endif //HERD_B200_CUDA_WORKER_GROUP_HPP

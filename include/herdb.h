@@ -112,13 +112,27 @@ void herdb_destroy(herdb_ctx* ctx);
 const char* herdb_strerror(int code);
 const char* herdb_last_error(const herdb_ctx* ctx);
 int  herdb_device_count(const herdb_ctx* ctx);
+/* host threads that run tasks (default 2, HERDB_TASK_THREADS): what an IWorkerGroup built on this context
+ * should answer to concurrent_workers() (i_worker_group.hpp:48; executor.cpp:96-113 keeps that many in flight) */
+int  herdb_task_threads(const herdb_ctx* ctx);
 
 /* ------------------------------------------------------------------ keys
  * load_key reads <key_dir>/<session>/<schema_type>.key (key_service.cpp:28-31);
  * load_key_mem takes the same blob from host memory; load_key_dev takes it from
  * device memory of ctx device `device` (e.g. after an NCCL broadcast done by the
- * caller, one process per GPU).  With n_devices > 1 the blob is uploaded to
- * device 0 and broadcast to the others over NVLink before conversion. */
+ * caller, one process per GPU).  With n_devices > 1 the blob is uploaded to the
+ * first device and reaches the others in one ncclBroadcast over NVLink / NVSwitch
+ * (SURVEY.md 2.1 K5); every device then converts its copy at the same time.
+ *
+ * Tasks (herdb_map_async / herdb_reduce_async) load the key of their session themselves
+ * and re-check the key FILE before every task: KeyService::add_key overwrites the file
+ * when a session uploads a key again and remove_key deletes it (key_service.cpp:19-60).
+ * A changed file (size / mtime / inode) is reloaded, a missing one fails the task.
+ * File-backed keys no task is using are evicted least-recently-used first once the key
+ * material per device exceeds HERDB_KEY_BUDGET_MB (default 32768; 324 MiB per STD128
+ * session) and come back from their file on the session's next task. */
+size_t herdb_key_blob_size(uint32_t n);     /* bytes of a key blob for LWE dimension n (herdb_params.h) */
+int herdb_loaded_keys(herdb_ctx* ctx);      /* sessions whose key is resident right now */
 int herdb_load_key(herdb_ctx* ctx, const char* session_uuid, int schema_type);
 int herdb_load_key_mem(herdb_ctx* ctx, const char* session_uuid, const void* blob, size_t len);
 int herdb_load_key_dev(herdb_ctx* ctx, const char* session_uuid, int device,
@@ -136,6 +150,7 @@ int herdb_key_lwe_n(herdb_ctx* ctx, const char* session_uuid, uint32_t* n_out);
 int herdb_map_async(herdb_ctx* ctx, const char* session_uuid,
                     const char* in_df_uuid, uint32_t in_partition, uint64_t row_count,
                     const char* out_df_uuid, uint32_t out_partition,
+                    int schema_type /* int(CryptoKeyPtr.schema_type): the key file is <schema_type>.key */,
                     const herdb_circuit* circuit, herdb_done_fn done, void* user);
 /* == IWorkerGroup::schedule_task(ReduceTask) (task.hpp:23-32, worker.proto:39-48; built at
  * execution_service.cpp:474-513).  The rows of all input partitions, in the order given, are folded to ONE
@@ -144,15 +159,19 @@ int herdb_map_async(herdb_ctx* ctx, const char* session_uuid,
  * tree, so the folding order is this backend's own [INFERRED]: a balanced pairwise tree, round by round
  * over the current list (0,1),(2,3),...; an odd last row is carried unchanged to the end of the next
  * list.  Every round is one batched evaluation of the circuit over all pairs (the same level-batched
- * kernels as a map task).  The output partition receives exactly one row. */
+ * kernels as a map task).  The output partition receives exactly one row.
+ * row_count of an input frame is a HINT: the reference labels the hidden frames of Policy::PARALLEL with
+ * row_count = partitions although each holds the one row a first-level reduce wrote
+ * (execution_service.cpp:613-618), so every input partition is read to its end and only the per-row length
+ * is validated. */
 typedef struct herdb_input_frame {
     const char* df_uuid;          /* InputDataFramePtr.pointer.uuid      (data_frame_ptr.hpp:15-19) */
     uint32_t    partition;        /* InputDataFramePtr.pointer.partition                            */
-    uint64_t    row_count;        /* InputDataFramePtr.row_count                                    */
+    uint64_t    row_count;        /* InputDataFramePtr.row_count (not trusted, see above)           */
 } herdb_input_frame;
 int herdb_reduce_async(herdb_ctx* ctx, const char* session_uuid,
                        const herdb_input_frame* inputs, size_t n_inputs,
-                       const char* out_df_uuid, uint32_t out_partition,
+                       const char* out_df_uuid, uint32_t out_partition, int schema_type,
                        const herdb_circuit* circuit, herdb_done_fn done, void* user);
 /* the same fold over host rows (n_rows >= 1 rows of out-row layout in, one row out) */
 int herdb_reduce_rows(herdb_ctx* ctx, const char* session_uuid, const herdb_circuit* circuit,
@@ -166,6 +185,8 @@ int herdb_wait_idle(herdb_ctx* ctx);
  * (lambda_http_worker_group.cpp:244-259 treats existence of the file as success). */
 int herdb_partition_read(const char* path, uint64_t row_count, size_t row_bytes, void* rows_out);
 int herdb_partition_write(const char* path, uint64_t row_count, size_t row_bytes, const void* rows);
+/* number of rows in a partition file whose rows all have `row_bytes` payload (reads to the end of the file) */
+int herdb_partition_count(const char* path, size_t row_bytes, uint64_t* rows_out);
 /* rows of partition k when `rows` rows are dealt to `partitions` files: rows/P + (k < rows%P)
  * (storage_service.cpp:121-129,328-331) */
 uint64_t herdb_partition_rows(uint64_t rows, uint32_t partitions, uint32_t k);
@@ -193,6 +214,12 @@ int herdb_eval_gate_batch_dev(herdb_ctx* ctx, const char* session_uuid, int devi
 int herdb_eval_circuit_rows_dev(herdb_ctx* ctx, const char* session_uuid, int device,
                                 const herdb_circuit* circuit,
                                 const uint16_t* d_rows_in, uint16_t* d_rows_out, size_t n_rows);
+/* herdb_eval_gate_batch_dev with the CTA shape forced: cts_per_cta = 4 (throughput shape), 2 or 1 (the small-job
+ * shapes a launch picks for tails and for batches that would leave SMs empty), 0 = the launch policy.  Measurement
+ * and parity tests of the shapes; every shape gives the same ciphertexts. */
+int herdb_eval_gate_batch_dev_shape(herdb_ctx* ctx, const char* session_uuid, int device, int gate,
+                                    const uint16_t* d_ct_a, const uint16_t* d_ct_b, uint16_t* d_ct_out,
+                                    size_t batch, int cts_per_cta);
 
 /* circuit facts (host-only, no device needed): bootstrapped gates per row, levels, slots */
 typedef struct herdb_circuit_info {
@@ -229,6 +256,8 @@ typedef struct herdb_stats {
     double   keyswitch_ms;          /* CUDA-event time of key-switch launches (sum)            */
     uint64_t blind_rotate_launches, keyswitch_launches;
     uint64_t h2d_bytes, d2h_bytes;
+    double   key_load_ms;           /* last key load: host blob -> kernel-ready keys on every device (wall clock) */
+    double   key_bcast_ms;          /* of which the NCCL broadcast to the other devices (0 on one device)         */
 } herdb_stats;
 int herdb_get_stats(herdb_ctx* ctx, int device, herdb_stats* out);
 /* the cudaStream_t (as void*) every kernel and copy of ctx device `device` is enqueued on, so a
@@ -238,19 +267,6 @@ int herdb_reset_stats(herdb_ctx* ctx);
 /* raw integer-pipe peak microbenchmark (IMAD / IADD3 / IMAD.HI / IMAD.WIDE), Tops/s */
 int herdb_measure_int_peak(herdb_ctx* ctx, int device, double* imad_tops, double* iadd3_tops,
                            double* imadhi_tops, double* imadwide_tops, double* mixed_tops);
-
-/* ------------------------------------------------------------------ client stand-in
- * herdsman never sees secret keys; the herd client (libherd, not in the
- * reference tree) generates keys and encrypts rows.  These host-only helpers
- * produce synthetic keys / ciphertexts in the flat formats of herdb_params.h so
- * benchmarks and tests have inputs.  They are NOT on the evaluation path. */
-size_t herdb_client_key_blob_size(uint32_t n);
-int herdb_client_keygen(uint32_t n, uint64_t seed, int8_t* sk_lwe /* n */, int8_t* sk_ring /* N */,
-                        void* blob, size_t blob_len);
-int herdb_client_encrypt_bits(uint32_t n, const int8_t* sk_lwe, uint64_t seed, uint64_t first_ct_index,
-                              const uint8_t* bits, size_t count, uint16_t* cts);
-int herdb_client_decrypt_bits(uint32_t n, const int8_t* sk_lwe, const uint16_t* cts, size_t count,
-                              uint8_t* bits);
 
 #ifdef __cplusplus
 }

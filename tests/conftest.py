@@ -8,6 +8,9 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+import clientsim as cs  # noqa: E402  (test infrastructure: synthetic herd-client keys and ciphertexts)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
@@ -23,12 +26,12 @@ def oracle_lib():
 def test_key():
     """n = 32 test parameter set: same ring / moduli / decomposition as STD128, 16x fewer CMUX steps"""
     from herdsman_b200 import api
-    sk, skr, blob = api.client_keygen(api.N_TEST, seed=0x48455244)
+    sk, skr, blob = cs.keygen(api.N_TEST, seed=0x48455244)
     return {"n": api.N_TEST, "sk": sk, "skr": skr, "blob": blob}
 
 
 @pytest.fixture(scope="session")
 def std128_key():
     from herdsman_b200 import api
-    sk, skr, blob = api.client_keygen(api.N_STD128, seed=0x48455244)
+    sk, skr, blob = cs.keygen(api.N_STD128, seed=0x48455244)
     return {"n": api.N_STD128, "sk": sk, "skr": skr, "blob": blob}

@@ -18,7 +18,6 @@ struct HostEnv {
     u32 tid() const { return tid_; }
     void sync() { pthread_barrier_wait(cta); }
     void syncwarp() { pthread_barrier_wait(&warps[tid_ >> 5]); }
-    V4 ldg_v4(const u32* p) const { return *reinterpret_cast<const V4*>(p); }
     // cp.async model that exposes both hazards: the destination is poisoned when the copy is issued (a
     // late reader of the old contents sees garbage) and filled only when a wait_group covers its group
     // (an early reader of the new contents sees garbage too)
@@ -44,7 +43,6 @@ struct HostEnv {
     void bulk_begin(unsigned long long*, u32) {}
     void bulk_copy(void* dst, const void* src, u32 bytes, unsigned long long*) { memcpy(dst, src, bytes); }
     void mbar_wait(unsigned long long*, u32) {}
-    void delay(u32) {}
 };
 
 template <int C> struct ThreadArg { HostEnv env; const BrParams* P; BrSmem<C>* S; u32 groups; };
@@ -58,7 +56,7 @@ template <int C> static void* thread_main(void* a) {
 template <int C>
 static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
                    u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
-    constexpr int kC = C; constexpr int kThreads = 64 * C;
+    constexpr int kC = C; constexpr int kThreads = (int)BrShape<C>::kThreads;
     const herdb_key_header* h = (const herdb_key_header*)blob;
     if (len < sizeof *h || h->magic != HERDB_KEY_MAGIC) return -1;
     const u32 n = h->n;
@@ -90,12 +88,12 @@ static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, cons
     GateDesc gd{}; gd.gate = (uint8_t)gate; gd.pool_a = 0; gd.pool_b = 1; gd.pool_out = 2;
     BrParams P{};
     P.bsk = bsk.data(); P.mono = mono.data(); P.ftw2 = ftw2.data(); P.itw1 = itw1.data(); P.gates = &gd;
-    P.pools[0] = Pool{const_cast<u16*>(ct_a), 1, 0};
-    P.pools[1] = Pool{const_cast<u16*>(ct_b), 1, 0};
+    P.pools[0] = Pool{const_cast<u16*>(ct_a), n + 1, 0};
+    P.pools[1] = Pool{const_cast<u16*>(ct_b), n + 1, 0};
     std::vector<u16> ext((size_t)batch * kExtStride);
-    P.ext = ext.data(); P.trace = trace_out; P.n = n; P.steps = steps; P.rows = batch; P.jobs = batch;
+    P.ext = ext.data(); P.trace = trace_out; P.n = n; P.steps = steps; P.rows = batch; P.jobs = batch; P.job0 = 0; P.job1 = batch;
     BrSmem<C>* S = new BrSmem<C>;
-    pthread_barrier_t cta, warps[2 * C];
+    pthread_barrier_t cta, warps[kThreads / 32];
     pthread_barrier_init(&cta, nullptr, kThreads);
     for (auto& w : warps) pthread_barrier_init(&w, nullptr, 32);
     std::vector<ThreadArg<C>> args(kThreads);
@@ -115,6 +113,14 @@ static int emu_run(const void* blob, size_t len, int gate, const u16* ct_a, cons
 extern "C" int emu_blind_rotate(const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
                                 u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
     return emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
+}
+// the small-job CTA shapes (C = 2, 1: whole key slice by bulk copy, 8 evaluation points per thread in phase B)
+extern "C" int emu_blind_rotate_shape(int shape, const void* blob, size_t len, int gate, const u16* ct_a, const u16* ct_b,
+                                      u32 batch, u32 steps, u16* ext_out, u32* trace_out) {
+    if (shape == 4) return emu_run<4>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
+    if (shape == 2) return emu_run<2>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
+    if (shape == 1) return emu_run<1>(blob, len, gate, ct_a, ct_b, batch, steps, ext_out, trace_out);
+    return -2;
 }
 
 // the FP64-pipe fold of phase B (modarith.cuh), host form, for the range / residue property test

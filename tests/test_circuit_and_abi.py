@@ -7,6 +7,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api, circuit as cm
+import clientsim as cs
 from oracle import pyoracle as po
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -36,9 +37,9 @@ def test_client_standin_matches_oracle_generator(test_key):
     sk2, skr2, blob2 = po.keygen(test_key["n"], 0x48455244)
     assert np.array_equal(test_key["blob"], blob2) and np.array_equal(test_key["sk"], sk2) and np.array_equal(test_key["skr"], skr2)
     bits = np.random.default_rng(0).integers(0, 2, 64).astype(np.uint8)
-    c1 = api.client_encrypt_bits(32, sk2, bits, seed=3, first=7)
+    c1 = cs.encrypt_bits(32, sk2, bits, seed=3, first=7)
     assert np.array_equal(c1, po.encrypt_bits(32, sk2, bits, seed=3, first=7))
-    assert np.array_equal(api.client_decrypt_bits(32, sk2, c1), bits)
+    assert np.array_equal(cs.decrypt_bits(32, sk2, c1), bits)
     assert np.array_equal(po.decrypt_bits(32, sk2, c1), bits)
 
 
@@ -98,9 +99,9 @@ def test_fast_xor_nodes_cost_one_bootstrap_and_decrypt(test_key):
     c = cm.adder_circuit(8, "fast")
     x = np.array([200, 13, 255]); y = np.array([100, 29, 255])
     bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
-    rows = api.client_encrypt_bits(test_key["n"], test_key["sk"], bits, seed=5)
+    rows = cs.encrypt_bits(test_key["n"], test_key["sk"], bits, seed=5)
     out = po.Oracle(test_key["blob"]).circuit_rows(c.to_c(), rows, 8)
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(test_key["n"], test_key["sk"], out)), (x + y) % 256)
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(test_key["n"], test_key["sk"], out)), (x + y) % 256)
 
 
 def test_not_and_constants_cost_no_bootstrap():
@@ -199,3 +200,40 @@ def test_reference_side_adapter_compiles_against_herdsman_headers(tmp_path):
     r = subprocess.run([cxx, "-std=c++20", "-fsyntax-only", "-Wall", "-I", str(tmp_path), "-I", ref + "/include",
                         "-I", ref + "/common/include", "-I", os.path.join(ROOT, "include"), str(src)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
+
+
+def test_partition_count_reads_to_the_end_of_the_file(tmp_path):
+    """reduce inputs: InputDataFramePtr.row_count is only a hint (the reference labels hidden frames with
+    row_count = partitions, execution_service.cpp:613-618), so a partition is read to its end"""
+    rows = np.arange(5 * 3 * 33, dtype=np.uint16).reshape(5, 3, 33)
+    api.partition_write(tmp_path / "p", rows)
+    assert api.partition_count(tmp_path / "p", 3, 32) == 5
+    api.partition_write(tmp_path / "e", rows[:0])
+    assert api.partition_count(tmp_path / "e", 3, 32) == 0
+    with pytest.raises(api.HerdbError):                          # other payload size
+        api.partition_count(tmp_path / "p", 2, 32)
+    raw = (tmp_path / "p").read_bytes()
+    (tmp_path / "t").write_bytes(raw[:-7])                        # truncated last row
+    with pytest.raises(api.HerdbError):
+        api.partition_count(tmp_path / "t", 3, 32)
+    with pytest.raises(api.HerdbError):
+        api.partition_count(tmp_path / "missing", 3, 32)
+
+
+def test_reference_reduce_tree_shapes():
+    """tests/reduce_trees.py restates ReduceStageProgress (execution_service.cpp:560-689)"""
+    import reduce_trees as rt
+    seq = rt.build("SEQUENCED", 3, [4, 4, 3], "in", "out", "hid")
+    assert seq == [([("in", 4, 0), ("in", 4, 1), ("in", 3, 2)], ("out", 1, 1))]
+    par = rt.build("PARALLEL", 3, [4, 4, 3], "in", "out", "hid")
+    assert len(par) == 4 and par[0] == ([("in", 4, 0)], ("hid", 3, 0))
+    assert par[-1] == ([("hid", 3, 0), ("hid", 3, 1), ("hid", 3, 2)], ("out", 1, 1))      # label 3, one row each
+    full = rt.build("PARALLEL_FULL", 5, [2] * 5, "in", "out", "hid", per_node_count=2)
+    # 5 leaves -> 2 pairs + 1 carried = 3 -> 1 pair + 1 carried = 2 -> output
+    assert len(full) == 5 + 2 + 1 + 1 and rt.hidden_partitions("PARALLEL_FULL", 5, 2) == 5 + 3 + 2
+    assert full[5] == ([("hid", 1, 0), ("hid", 1, 1)], ("hid", 1, 5)) and full[7][0] == [("hid", 1, 5), ("hid", 1, 6)]
+    assert full[-1] == ([("hid", 1, 7), ("hid", 1, 4)], ("out", 1, 1))
+    produced = set()
+    for ins, out in full:                                         # every input exists when its task runs
+        assert all(n[0] == "in" or n in produced for n in ins)
+        produced.add(out)

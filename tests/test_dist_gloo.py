@@ -20,11 +20,12 @@ def _worker(rank, world, port, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from herdsman_b200 import api, circuit as cm, sharding
+    import clientsim as cs
     from oracle import pyoracle as po
     n = api.N_TEST
     blob = sk = None
     if rank == 0:
-        sk, skr, blob = api.client_keygen(n)
+        sk, skr, blob = cs.keygen(n)
     t = sharding.broadcast_blob(blob, dist)                       # key blob: one broadcast, then no collective
     blob = t.numpy()
     digest = hashlib.sha256(blob.tobytes()).hexdigest()
@@ -33,7 +34,7 @@ def _worker(rank, world, port, q):
     c = cm.single_gate_circuit(cm.Operation.NAND)
     n_rows = 7                                                     # ragged: 4 + 3
     bits = np.random.default_rng(0).integers(0, 2, (n_rows, 2)).astype(np.uint8)
-    rows = api.client_encrypt_bits(n, sk, bits, seed=5)           # same on every rank (deterministic generator)
+    rows = cs.encrypt_bits(n, sk, bits, seed=5)           # same on every rank (deterministic generator)
     lo, hi = sharding.row_slice(n_rows, world, rank)
     orc = po.Oracle(blob)
     local = orc.circuit_rows(c.to_c(), rows[lo:hi], 1)

@@ -19,14 +19,15 @@ def emu():
     subprocess.run(["make", "-C", EMU_DIR], check=True, capture_output=True)
     L = C.CDLL(os.path.join(EMU_DIR, "libemu.so"))
     L.emu_blind_rotate.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
+    L.emu_blind_rotate_shape.argtypes = [C.c_int] + L.emu_blind_rotate.argtypes
     return L
 
 
-def _run(emu, blob, gate, ca, cb, steps):
+def _run(emu, blob, gate, ca, cb, steps, shape=4):
     B = ca.shape[0]
     ext = np.zeros((B, 1025), np.uint16); trace = np.zeros((B, 2, 1024), np.uint32)
-    rc = emu.emu_blind_rotate(blob.ctypes.data, blob.size, po.GATE[gate], ca.ctypes.data, cb.ctypes.data, B, steps,
-                              ext.ctypes.data, trace.ctypes.data)
+    rc = emu.emu_blind_rotate_shape(shape, blob.ctypes.data, blob.size, po.GATE[gate], ca.ctypes.data, cb.ctypes.data, B, steps,
+                                    ext.ctypes.data, trace.ctypes.data)
     assert rc == 0
     return ext, trace
 
@@ -43,6 +44,24 @@ def test_emulated_kernel_body_matches_oracle(emu, test_key, gate, steps):
     ext, trace = _run(emu, blob, gate, ca, cb, steps)
     for i in range(B):
         assert np.array_equal(o.blind_rotate_trace(gate, ca[i], cb[i], steps).reshape(2, 1024), trace[i]), (gate, steps, i)
+        if steps == n:
+            assert np.array_equal(o.bootstrap_extract(gate, ca[i], cb[i]), ext[i])
+
+
+@pytest.mark.parametrize("shape,gate,steps", [(2, "NAND", 0), (2, "NAND", 3), (2, "OR", 32), (2, "XOR_FAST", 32),
+                                              (1, "NAND", 1), (1, "AND", 32), (1, "XNOR_FAST", 32)])
+def test_emulated_small_job_shapes_match_oracle(emu, test_key, shape, gate, steps):
+    """the C = 2 and C = 1 CTA shapes (128 threads, whole key slice staged by bulk copy, two chunks of evaluation
+    points per thread in phase B; at C = 1 warps 2 and 3 have no polynomial in phase A)"""
+    n, sk, blob = test_key["n"], test_key["sk"], test_key["blob"]
+    o = po.Oracle(blob)
+    rng = np.random.default_rng(6)
+    B = 3                                              # C = 2: a full group and a ragged one
+    a = rng.integers(0, 2, B).astype(np.uint8); b = rng.integers(0, 2, B).astype(np.uint8)
+    ca = po.encrypt_bits(n, sk, a, first=0); cb = po.encrypt_bits(n, sk, b, first=100)
+    ext, trace = _run(emu, blob, gate, ca, cb, steps, shape)
+    for i in range(B):
+        assert np.array_equal(o.blind_rotate_trace(gate, ca[i], cb[i], steps).reshape(2, 1024), trace[i]), (shape, gate, steps, i)
         if steps == n:
             assert np.array_equal(o.bootstrap_extract(gate, ca[i], cb[i]), ext[i])
 

@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api, circuit as cm
+import clientsim as cs
 
 pytestmark = pytest.mark.gpu
 
@@ -25,7 +26,7 @@ def sess(backend, std128_key, oracle_lib):
 
 def _enc_words(s, cols, bits, seed):
     mats = [cm.pack_words(c, b) for c, b in zip(cols, bits)]
-    return api.client_encrypt_bits(s["n"], s["sk"], np.concatenate(mats, axis=1), seed=seed)
+    return cs.encrypt_bits(s["n"], s["sk"], np.concatenate(mats, axis=1), seed=seed)
 
 
 def test_config3_compare32_rows_and_split_invariance(backend, sess):
@@ -40,7 +41,7 @@ def test_config3_compare32_rows_and_split_invariance(backend, sess):
     rows_in = _enc_words(s, (x, y), (32, 32), seed=3)
     out = backend.eval_circuit_rows(s["name"], c, rows_in)
     assert out.shape == (rows, 1, s["n"] + 1)
-    dec = api.client_decrypt_bits(s["n"], s["sk"], out).reshape(rows)
+    dec = cs.decrypt_bits(s["n"], s["sk"], out).reshape(rows)
     assert np.array_equal(dec, (x < (y & 0xFFFFFFFF)).astype(dec.dtype))
     # row sharding: two "devices" with contiguous slices give byte-identical rows
     k = rows // 3
@@ -62,7 +63,7 @@ def test_config4_multiply32_rows(backend, sess):
     y = np.array([0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 3, 987654321, 0xCAFEBABE, 0xFFFF0000, 2], np.uint64)
     rows_in = _enc_words(s, (x, y), (32, 32), seed=4)
     out = backend.eval_circuit_rows(s["name"], c, rows_in)
-    dec = cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out))
+    dec = cm.unpack_words(cs.decrypt_bits(s["n"], s["sk"], out))
     assert np.array_equal(dec.reshape(rows), (x * y) & 0xFFFFFFFF)
     # bit-exact on >= 8 rows (8 x 4,746 bootstraps in the oracle, ~2 minutes on 16 host cores)
     ref = s["oracle"].circuit_rows(c.to_c(), rows_in, c.out_bits)
@@ -82,7 +83,7 @@ def test_config5_pipeline_stages_equal_fused_plaintext(backend, sess):
     s2 = backend.eval_circuit_rows(s["name"], cm.compare_circuit(8), np.concatenate([s1, abd[:, 16:]], axis=1))   # (a+b) < d
     s3 = backend.eval_circuit_rows(s["name"], cm.select_circuit(8), np.concatenate([s2, s1, abd[:, 16:]], axis=1))
     assert s3.shape == (rows, 8, w)
-    got = cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], s3)).reshape(rows)
+    got = cm.unpack_words(cs.decrypt_bits(s["n"], s["sk"], s3)).reshape(rows)
     sm = (a + b) % 256
     assert np.array_equal(got, np.where(sm < d, sm, d))
     # every stage bit-exact with the oracle's per-row interpreter on its first 6 rows
@@ -99,7 +100,7 @@ def test_config5_pipeline_stages_equal_fused_plaintext(backend, sess):
     assert np.array_equal(piped, s3)
     # the fused single-stage circuit decrypts to the same plaintext
     fused = backend.eval_circuit_rows(s["name"], cm.pipeline_circuit(8), abd)
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], fused)).reshape(rows), got)
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(s["n"], s["sk"], fused)).reshape(rows), got)
 
 
 def test_config2_gate_batch_is_deterministic_and_order_free(backend, sess):
@@ -108,11 +109,11 @@ def test_config2_gate_batch_is_deterministic_and_order_free(backend, sess):
     rng = np.random.default_rng(2)
     B = 1500
     a = rng.integers(0, 2, B).astype(np.uint8); b = rng.integers(0, 2, B).astype(np.uint8)
-    ca = api.client_encrypt_bits(s["n"], s["sk"], a, seed=2, first=0)
-    cb = api.client_encrypt_bits(s["n"], s["sk"], b, seed=2, first=1 << 22)
+    ca = cs.encrypt_bits(s["n"], s["sk"], a, seed=2, first=0)
+    cb = cs.encrypt_bits(s["n"], s["sk"], b, seed=2, first=1 << 22)
     out = backend.eval_gate_batch(s["name"], "NAND", ca, cb)
     perm = rng.permutation(B)
     out_p = backend.eval_gate_batch(s["name"], "NAND", ca[perm], cb[perm])
     assert np.array_equal(out_p, out[perm])
     assert np.array_equal(backend.eval_gate_batch(s["name"], "NAND", ca[:7], cb[:7]), out[:7])
-    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
+    assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))

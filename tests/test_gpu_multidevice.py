@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api, circuit as cm
+import clientsim as cs
 
 pytestmark = pytest.mark.gpu
 
@@ -47,7 +48,7 @@ def test_rows_and_partition_file_identical_on_G_devices(tmp_path, std128_key, or
     rng = np.random.default_rng(3)
     x = rng.integers(0, 1 << 32, rows_n, dtype=np.uint64); y = rng.integers(0, 1 << 32, rows_n, dtype=np.uint64)
     y[:3] = x[:3]
-    rows = api.client_encrypt_bits(k["n"], k["sk"], np.concatenate([cm.pack_words(x, 32), cm.pack_words(y, 32)], axis=1), seed=3)
+    rows = cs.encrypt_bits(k["n"], k["sk"], np.concatenate([cm.pack_words(x, 32), cm.pack_words(y, 32)], axis=1), seed=3)
     wg1, s1, st1 = _world(tmp_path / "one", k, (0,))
     try:
         raw1, out1 = _run_map(wg1, s1, st1, c, rows, k["n"])
@@ -64,7 +65,7 @@ def test_rows_and_partition_file_identical_on_G_devices(tmp_path, std128_key, or
     assert all(s["gates_bootstrapped"] > 0 for s in stats), "every device must have evaluated its slice"
     assert hashlib.sha256(raw1).hexdigest() == hashlib.sha256(rawG).hexdigest()          # output partition file, byte for byte
     assert np.array_equal(out1, outG) and np.array_equal(host1, hostG) and np.array_equal(host1, out1)
-    dec = api.client_decrypt_bits(k["n"], k["sk"], outG).reshape(rows_n)
+    dec = cs.decrypt_bits(k["n"], k["sk"], outG).reshape(rows_n)
     assert np.array_equal(dec, (x < y).astype(dec.dtype))
     orc = oracle_lib.Oracle(k["blob"])
     sample = np.r_[0:4, rows_n - 4:rows_n]                # first slice and last slice
@@ -78,8 +79,8 @@ def test_pipeline_and_reduce_identical_on_two_devices(tmp_path, test_key):
     rng = np.random.default_rng(9)
     rows_n = 23
     a = rng.integers(0, 256, rows_n); b = rng.integers(0, 256, rows_n); t = rng.integers(0, 256, rows_n)
-    rows = api.client_encrypt_bits(k["n"], k["sk"], np.concatenate([cm.pack_words(v, 8) for v in (a, b, t)], axis=1), seed=9)
-    red = api.client_encrypt_bits(k["n"], k["sk"], cm.pack_words(a, 8), seed=10)
+    rows = cs.encrypt_bits(k["n"], k["sk"], np.concatenate([cm.pack_words(v, 8) for v in (a, b, t)], axis=1), seed=9)
+    red = cs.encrypt_bits(k["n"], k["sk"], cm.pack_words(a, 8), seed=10)
     outs = []
     for devs in [(0,), (0, 1), (1, 0)]:
         be = api.Backend(devices=devs)
@@ -91,4 +92,4 @@ def test_pipeline_and_reduce_identical_on_two_devices(tmp_path, test_key):
     for p, r in outs[1:]:
         assert np.array_equal(p, outs[0][0]) and np.array_equal(r, outs[0][1])
     s = (a + b) % 256
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(k["n"], k["sk"], outs[0][0])), np.where(s < t, s, t))
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(k["n"], k["sk"], outs[0][0])), np.where(s < t, s, t))

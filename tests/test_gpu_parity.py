@@ -4,6 +4,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api, circuit as cm
+import clientsim as cs
 
 pytestmark = pytest.mark.gpu
 
@@ -34,8 +35,8 @@ def std_session(backend, std128_key, oracle_lib):
 def _inputs(sess, batch, seed):
     rng = np.random.default_rng(seed)
     a = rng.integers(0, 2, batch).astype(np.uint8); b = rng.integers(0, 2, batch).astype(np.uint8)
-    ca = api.client_encrypt_bits(sess["n"], sess["sk"], a, seed=seed, first=0)
-    cb = api.client_encrypt_bits(sess["n"], sess["sk"], b, seed=seed, first=1 << 20)
+    ca = cs.encrypt_bits(sess["n"], sess["sk"], a, seed=seed, first=0)
+    cb = cs.encrypt_bits(sess["n"], sess["sk"], b, seed=seed, first=1 << 20)
     return a, b, ca, cb
 
 
@@ -46,7 +47,7 @@ def test_gate_bit_exact_test_params(backend, test_session, gate):
     out = backend.eval_gate_batch(s["name"], gate, ca, cb)
     ref = s["oracle"].gate(gate, ca, cb)
     assert np.array_equal(out, ref)
-    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), PLAIN[gate](a, b))
+    assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out), PLAIN[gate](a, b))
 
 
 @pytest.mark.parametrize("batch", [1, 2, 3, 4, 5, 592, 593, 1200])
@@ -54,7 +55,7 @@ def test_gate_batch_sizes(backend, test_session, batch):
     s = test_session
     a, b, ca, cb = _inputs(s, batch, seed=batch)
     out = backend.eval_gate_batch(s["name"], "NAND", ca, cb)
-    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
+    assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
     k = min(batch, 24)
     assert np.array_equal(out[:k], s["oracle"].gate("NAND", ca[:k], cb[:k]))
     assert np.array_equal(out[-k:], s["oracle"].gate("NAND", ca[-k:], cb[-k:]))
@@ -67,7 +68,7 @@ def test_gate_batch_pipelined_pieces(backend, test_session, batch):
     s = test_session
     a, b, ca, cb = _inputs(s, batch, seed=batch)
     out = backend.eval_gate_batch(s["name"], "OR", ca, cb)
-    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), a | b)
+    assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out), a | b)
     assert np.array_equal(out, s["oracle"].gate("OR", ca, cb))
 
 
@@ -85,7 +86,7 @@ def test_gate_bit_exact_std128(backend, std_session, gate):
     out = backend.eval_gate_batch(s["name"], gate, ca, cb)
     ref = s["oracle"].gate(gate, ca, cb)
     assert np.array_equal(out, ref), gate
-    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), PLAIN[gate](a, b))
+    assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out), PLAIN[gate](a, b))
 
 
 def test_std128_large_batch_decrypts(backend, std_session):
@@ -94,10 +95,10 @@ def test_std128_large_batch_decrypts(backend, std_session):
     s = std_session
     a, b, ca, cb = _inputs(s, 2048, seed=9)
     out = backend.eval_gate_batch(s["name"], "NAND", ca, cb)
-    d1 = api.client_decrypt_bits(s["n"], s["sk"], out)
+    d1 = cs.decrypt_bits(s["n"], s["sk"], out)
     assert np.array_equal(d1, 1 - (a & b))
     out2 = backend.eval_gate_batch(s["name"], "OR", out, ca)
-    assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out2), d1 | a)
+    assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out2), d1 | a)
 
 
 @pytest.mark.parametrize("name,build,bits_in,plain", [
@@ -115,9 +116,9 @@ def test_circuit_bit_exact_test_params(backend, test_session, name, build, bits_
     rng = np.random.default_rng(3)
     x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
     bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
-    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=21)
+    rows_in = cs.encrypt_bits(s["n"], s["sk"], bits, seed=21)
     out = backend.eval_circuit_rows(s["name"], c, rows_in)
-    dec = api.client_decrypt_bits(s["n"], s["sk"], out)
+    dec = cs.decrypt_bits(s["n"], s["sk"], out)
     assert np.array_equal(cm.unpack_words(dec), plain(x, y))
     ref = s["oracle"].circuit_rows(c.to_c(), rows_in, c.out_bits)
     assert np.array_equal(out, ref)
@@ -133,11 +134,11 @@ def test_circuit_constants_and_not_outputs(backend, test_session):
     c.output_bit(0, 4, c.and_(a, one)); c.output_bit(0, 5, c.or_(c.not_(b), zero)); c.output_bit(0, 6, c.nand(a, b))
     c.output_bit(0, 7, c.mux(a, b, c.not_(b)))
     bits = np.array([[0, 0], [0, 1], [1, 0], [1, 1]], np.uint8)
-    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=33)
+    rows_in = cs.encrypt_bits(s["n"], s["sk"], bits, seed=33)
     out = backend.eval_circuit_rows(s["name"], c, rows_in)
     ref = s["oracle"].circuit_rows(c.to_c(), rows_in, 8)
     assert np.array_equal(out, ref)
-    dec = api.client_decrypt_bits(s["n"], s["sk"], out)
+    dec = cs.decrypt_bits(s["n"], s["sk"], out)
     A, B = bits[:, 0], bits[:, 1]
     want = np.stack([A, 1 - A, np.ones(4, int), np.zeros(4, int), A, 1 - B, 1 - (A & B), np.where(A == 1, B, 1 - B)], axis=1)
     assert np.array_equal(dec, want)
@@ -150,9 +151,9 @@ def test_add8_std128_rows(backend, std_session):
     rng = np.random.default_rng(1)
     x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
     bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
-    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=1)
+    rows_in = cs.encrypt_bits(s["n"], s["sk"], bits, seed=1)
     out = backend.eval_circuit_rows(s["name"], c, rows_in)
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out)), (x + y) % 256)
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(s["n"], s["sk"], out)), (x + y) % 256)
     ref = s["oracle"].circuit_rows(c.to_c(), rows_in[:16], c.out_bits)     # oracle: ~3 s per row per core, OpenMP over rows
     assert np.array_equal(out[:16], ref)
 
@@ -174,9 +175,9 @@ def test_rescheduled_levels_bit_exact(backend, test_session, name, build, plain)
     rng = np.random.default_rng(8)
     x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
     bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
-    rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=77)
+    rows_in = cs.encrypt_bits(s["n"], s["sk"], bits, seed=77)
     out = backend.eval_circuit_rows(s["name"], c, rows_in)
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], out)), plain(x, y))
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(s["n"], s["sk"], out)), plain(x, y))
     ref = s["oracle"].circuit_rows(c.to_c(), rows_in[:6], c.out_bits)
     assert np.array_equal(out[:6], ref)
     small = backend.eval_circuit_rows(s["name"], c, rows_in[:5])                  # 5 rows: as-soon-as-possible levels
@@ -196,18 +197,18 @@ def test_small_memory_budget_chunks_rows_and_batches(backend, test_session, monk
         rng = np.random.default_rng(12)
         x = rng.integers(0, 256, rows); y = rng.integers(0, 256, rows)
         bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
-        rows_in = api.client_encrypt_bits(s["n"], s["sk"], bits, seed=5)
+        rows_in = cs.encrypt_bits(s["n"], s["sk"], bits, seed=5)
         small.reset_stats()
         got = small.eval_circuit_rows("tiny", c, rows_in)
         assert small.stats()["blind_rotate_launches"] > api.analyze(c)["levels"]        # really chunked
         assert np.array_equal(got, backend.eval_circuit_rows(s["name"], c, rows_in))
-        assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(s["n"], s["sk"], got)), (x + y) % 256)
+        assert np.array_equal(cm.unpack_words(cs.decrypt_bits(s["n"], s["sk"], got)), (x + y) % 256)
         a, b, ca, cb = _inputs(s, 2500, seed=3)
         small.reset_stats()
         out = small.eval_gate_batch("tiny", "NAND", ca, cb)
         assert small.stats()["blind_rotate_launches"] >= 5
         assert np.array_equal(out, backend.eval_gate_batch(s["name"], "NAND", ca, cb))
-        assert np.array_equal(api.client_decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
+        assert np.array_equal(cs.decrypt_bits(s["n"], s["sk"], out), 1 - (a & b))
     finally:
         small.close()
 
@@ -220,7 +221,7 @@ def test_concurrent_callers_share_a_device(backend, test_session):
     c = cm.adder_circuit(8)
     rng = np.random.default_rng(14)
     x = rng.integers(0, 256, 12); y = rng.integers(0, 256, 12)
-    rows_in = api.client_encrypt_bits(s["n"], s["sk"], np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1), seed=6)
+    rows_in = cs.encrypt_bits(s["n"], s["sk"], np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1), seed=6)
     a, b, ca, cb = _inputs(s, 700, seed=15)
     want_rows = backend.eval_circuit_rows(s["name"], c, rows_in)
     want_gate = backend.eval_gate_batch(s["name"], "AND", ca, cb)

@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api, circuit as cm
+import clientsim as cs
 
 pytestmark = pytest.mark.gpu
 
@@ -49,7 +50,7 @@ def test_map_tasks_over_partitions_match_oracle(world):
     rng = np.random.default_rng(0)
     x = rng.integers(0, 256, n_rows); y = rng.integers(0, 256, n_rows)
     bits = np.concatenate([cm.pack_words(x, 8), cm.pack_words(y, 8)], axis=1)
-    rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=40)
+    rows = cs.encrypt_bits(w["n"], w["sk"], bits, seed=40)
     in_df = _frame(w, rows, parts)
     out_df = str(uuid.uuid4())
     (w["storage"] / w["session"] / out_df).mkdir(parents=True)   # ExecutionService creates the output frame dir
@@ -65,7 +66,7 @@ def test_map_tasks_over_partitions_match_oracle(world):
     got = np.concatenate([api.partition_read(w["storage"] / w["session"] / out_df / str(k), api.partition_rows(n_rows, parts, k), 8, w["n"])
                           for k in range(parts)])
     assert not list((w["storage"] / w["session"] / out_df).glob("*.tmp"))
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got)), (x + y) % 256)
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(w["n"], w["sk"], got)), (x + y) % 256)
     assert np.array_equal(got, w["oracle"].circuit_rows(c.to_c(), rows, 8))       # bit-exact with the per-row interpreter
 
 
@@ -85,7 +86,7 @@ def test_chained_map_stages(world):
     s2.output_bit(0, 0, cm._less_than(s2, xs, ys, "wire")); s2.output_word(1, xs); s2.output_word(2, ys)
     s3 = cm.select_circuit(8)
     bits = np.concatenate([cm.pack_words(a, 8), cm.pack_words(b, 8), cm.pack_words(t, 8)], axis=1)
-    rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=41)
+    rows = cs.encrypt_bits(w["n"], w["sk"], bits, seed=41)
     df = _frame(w, rows, 1)
     ref = rows
     for c in (s1, s2, s3):
@@ -96,7 +97,7 @@ def test_chained_map_stages(world):
     got = api.partition_read(w["storage"] / w["session"] / df / "0", n_rows, 8, w["n"])
     assert np.array_equal(got, ref)
     s = (a + b) % 256
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got)), np.where(s < t, s, t))
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(w["n"], w["sk"], got)), np.where(s < t, s, t))
 
 
 def test_empty_partition_and_error_statuses(world):
@@ -110,7 +111,7 @@ def test_empty_partition_and_error_statuses(world):
     assert w["wg"].schedule_task(_task(w, c, in_df, out_df, 7, 1)).wait(120) == api.TaskHandle.Status.ERROR
     assert w["wg"].schedule_task(_task(w, c, in_df, out_df, 0, 3)).wait(120) == api.TaskHandle.Status.ERROR
     add = cm.adder_circuit(8)
-    rows = api.client_encrypt_bits(w["n"], w["sk"], np.zeros((2, 2), np.uint8), seed=42)
+    rows = cs.encrypt_bits(w["n"], w["sk"], np.zeros((2, 2), np.uint8), seed=42)
     df2 = _frame(w, rows, 1)
     assert w["wg"].schedule_task(_task(w, add, df2, out_df, 0, 2)).wait(120) == api.TaskHandle.Status.ERROR
     bad = _task(w, c, df2, out_df, 0, 2); bad.session_uuid = str(uuid.uuid4())
@@ -138,14 +139,14 @@ def test_reduce_task_over_partitions_matches_oracle(world):
     c = cm.reduce_add_circuit(8)
     n_rows, parts = 7, 3                                         # 3 + 2 + 2 rows, odd counts in the tree
     vals = np.random.default_rng(5).integers(0, 256, n_rows)
-    rows = api.client_encrypt_bits(w["n"], w["sk"], cm.pack_words(vals, 8), seed=43)
+    rows = cs.encrypt_bits(w["n"], w["sk"], cm.pack_words(vals, 8), seed=43)
     in_df = _frame(w, rows, parts)
     out_df = str(uuid.uuid4()); (w["storage"] / w["session"] / out_df).mkdir(parents=True)
     ptrs = [api.InputDataFramePtr(api.DataFramePtr(in_df, k), api.partition_rows(n_rows, parts, k)) for k in range(parts)]
     task = api.ReduceTask(w["session"], ptrs, api.DataFramePtr(out_df, 0), api.CryptoKeyPtr(1), c)
     assert w["wg"].schedule_task(task).wait(300) == api.TaskHandle.Status.COMPLETED
     got = api.partition_read(w["storage"] / w["session"] / out_df / "0", 1, 8, w["n"])
-    assert cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got))[0] == vals.sum() % 256
+    assert cm.unpack_words(cs.decrypt_bits(w["n"], w["sk"], got))[0] == vals.sum() % 256
     assert np.array_equal(got, _oracle_tree_fold(w["oracle"], c, rows))           # bit-exact, same folding order
     # a single input row passes through unchanged; a map-shaped circuit is refused
     one = _frame(w, rows[:1], 1)
@@ -162,9 +163,9 @@ def test_reduce_rows_max(world):
     w = world
     c = cm.reduce_max_circuit(8)
     vals = np.random.default_rng(6).integers(0, 256, 6)
-    rows = api.client_encrypt_bits(w["n"], w["sk"], cm.pack_words(vals, 8), seed=44)
+    rows = cs.encrypt_bits(w["n"], w["sk"], cm.pack_words(vals, 8), seed=44)
     got = w["wg"].backend.reduce_rows(w["session"], c, rows)
-    assert cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got))[0] == vals.max()
+    assert cm.unpack_words(cs.decrypt_bits(w["n"], w["sk"], got))[0] == vals.max()
     assert np.array_equal(got, _oracle_tree_fold(w["oracle"], c, rows))
 
 
@@ -177,7 +178,7 @@ def test_pipeline_rows_keep_intermediates_on_device(world):
     a = rng.integers(0, 256, n_rows); b = rng.integers(0, 256, n_rows); t = rng.integers(0, 256, n_rows)
     s1, s2, s3 = cm.pipeline_stages(8)
     bits = np.concatenate([cm.pack_words(a, 8), cm.pack_words(b, 8), cm.pack_words(t, 8)], axis=1)
-    rows = api.client_encrypt_bits(w["n"], w["sk"], bits, seed=45)
+    rows = cs.encrypt_bits(w["n"], w["sk"], bits, seed=45)
     be = w["wg"].backend
     be.load_key(w["session"])
     got = be.eval_pipeline_rows(w["session"], [s1, s2, s3], rows)
@@ -186,6 +187,6 @@ def test_pipeline_rows_keep_intermediates_on_device(world):
         ref = w["oracle"].circuit_rows(c.to_c(), ref, c.out_bits)
     assert np.array_equal(got, ref)
     s = (a + b) % 256
-    assert np.array_equal(cm.unpack_words(api.client_decrypt_bits(w["n"], w["sk"], got)), np.where(s < t, s, t))
+    assert np.array_equal(cm.unpack_words(cs.decrypt_bits(w["n"], w["sk"], got)), np.where(s < t, s, t))
     with pytest.raises(api.HerdbError):                          # stage 2 does not take stage 1's row
         be.eval_pipeline_rows(w["session"], [s1, s3], rows)

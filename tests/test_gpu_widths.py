@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api, circuit as cm
+import clientsim as cs
 
 pytestmark = pytest.mark.gpu
 D = cm.DataType
@@ -45,11 +46,11 @@ def test_every_data_type_width(env, t):
     if bits == 64:
         x[0] |= 1 << 63; y[1] |= 1 << 63
     mat = np.array([[(v >> i) & 1 for i in range(bits)] + [(w >> i) & 1 for i in range(bits)] for v, w in zip(x, y)], np.uint8)
-    rows_in = api.client_encrypt_bits(e["n"], e["sk"], mat, seed=60 + int(t))
+    rows_in = cs.encrypt_bits(e["n"], e["sk"], mat, seed=60 + int(t))
     out = e["be"].eval_circuit_rows("w", c, rows_in)
     assert out.shape == (rows, bits, e["n"] + 1)
     assert np.array_equal(out, e["oracle"].circuit_rows(c.to_c(), rows_in, bits))
-    dec = api.client_decrypt_bits(e["n"], e["sk"], out)
+    dec = cs.decrypt_bits(e["n"], e["sk"], out)
     got = [sum(int(dec[r, i]) << i for i in range(bits)) for r in range(rows)]
     assert got == [_plain_bitwise(v, w, bits) for v, w in zip(x, y)]
 
@@ -61,10 +62,10 @@ def test_wide_adders_16_and_64(env):
                        (64, [0xFFFFFFFFFFFFFFFF, 0x0123456789ABCDEF, 1 << 63], [1, 0xFEDCBA9876543211, 1 << 63])]:
         c = cm.adder_circuit(bits)
         mat = np.array([[(v >> i) & 1 for i in range(bits)] + [(w >> i) & 1 for i in range(bits)] for v, w in zip(x, y)], np.uint8)
-        rows_in = api.client_encrypt_bits(e["n"], e["sk"], mat, seed=70 + bits)
+        rows_in = cs.encrypt_bits(e["n"], e["sk"], mat, seed=70 + bits)
         out = e["be"].eval_circuit_rows("w", c, rows_in)
         assert np.array_equal(out, e["oracle"].circuit_rows(c.to_c(), rows_in, bits))
-        dec = api.client_decrypt_bits(e["n"], e["sk"], out)
+        dec = cs.decrypt_bits(e["n"], e["sk"], out)
         assert [sum(int(dec[r, i]) << i for i in range(bits)) for r in range(len(x))] == [(v + w) % (1 << bits) for v, w in zip(x, y)]
 
 
@@ -81,10 +82,10 @@ def test_mixed_width_row_field_offsets(env):
     rng = np.random.default_rng(77)
     rows = 4
     mat = rng.integers(0, 2, (rows, c.in_bits)).astype(np.uint8)
-    rows_in = api.client_encrypt_bits(e["n"], e["sk"], mat, seed=78)
+    rows_in = cs.encrypt_bits(e["n"], e["sk"], mat, seed=78)
     out = e["be"].eval_circuit_rows("w", c, rows_in)
     assert np.array_equal(out, e["oracle"].circuit_rows(c.to_c(), rows_in, c.out_bits))
-    dec = api.client_decrypt_bits(e["n"], e["sk"], out)
+    dec = cs.decrypt_bits(e["n"], e["sk"], out)
     sel, w16, w64, w8 = mat[:, 0:1], mat[:, 1:17], mat[:, 17:81], mat[:, 81:89]
     want = np.concatenate([sel & w8, (w16[:, 15:16] | w64[:, 63:64]),
                            np.concatenate([w64[:, :32] | np.tile(w16, (1, 2)), 1 - w64[:, 32:]], axis=1)], axis=1)

@@ -11,6 +11,7 @@ import numpy as np
 import pytest
 
 from herdsman_b200 import api
+import clientsim as cs
 from oracle import pyoracle as po
 
 N, Q, QLWE, QKS, BG, DG, BKS, DKS = 1024, (1 << 27) - (1 << 11) + 1, 1024, 1 << 14, 128, 4, 128, 2
@@ -109,11 +110,11 @@ def test_schoolbook_restatement_agrees_with_oracle(test_key, gate):
     assert n == test_key["n"]
     orc = po.Oracle(test_key["blob"])
     bits_a = np.array([0, 1, 1], np.uint8); bits_b = np.array([1, 1, 0], np.uint8)
-    ca = api.client_encrypt_bits(n, test_key["sk"], bits_a, seed=91, first=0)
-    cb = api.client_encrypt_bits(n, test_key["sk"], bits_b, seed=91, first=100)
+    ca = cs.encrypt_bits(n, test_key["sk"], bits_a, seed=91, first=0)
+    cb = cs.encrypt_bits(n, test_key["sk"], bits_b, seed=91, first=100)
     ref = orc.gate(gate, ca, cb)
     for k in range(len(bits_a)):
         got = eval_bin_gate(gate, n, bsk, ksk, ca[k], cb[k])
         assert np.array_equal(got, ref[k]), "schoolbook restatement and oracle.c differ"
     plain = {"NAND": 1 - (bits_a & bits_b), "OR": bits_a | bits_b, "XOR_FAST": bits_a ^ bits_b}[gate]
-    assert np.array_equal(api.client_decrypt_bits(n, test_key["sk"], ref), plain)
+    assert np.array_equal(cs.decrypt_bits(n, test_key["sk"], ref), plain)

@@ -25,13 +25,14 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from herdsman_b200 import api, circuit as cm  # noqa: E402
+import clientsim as cs
 
 N = 512
 
 
 def enc_words(sk, cols, bits, seed):
     mats = [cm.pack_words(c, b) for c, b in zip(cols, bits)]
-    return api.client_encrypt_bits(N, sk, np.concatenate(mats, axis=1), seed=seed)
+    return cs.encrypt_bits(N, sk, np.concatenate(mats, axis=1), seed=seed)
 
 
 def run_circuit(be, sk, name, circ, cols, bits, plain, seed, oracle_rows, orc):
@@ -48,7 +49,7 @@ def run_circuit(be, sk, name, circ, cols, bits, plain, seed, oracle_rows, orc):
         spent += d
         if dt is None or d < dt:
             dt, st = d, be.stats()
-    dec = cm.unpack_words(api.client_decrypt_bits(N, sk, out)).reshape(rows)
+    dec = cm.unpack_words(cs.decrypt_bits(N, sk, out)).reshape(rows)
     ok = bool(np.array_equal(dec, plain))
     sm = be.device_sm_count() if hasattr(be, "device_sm_count") else 148
     sched = api.schedule(circ, rows, sm * 4)
@@ -81,7 +82,7 @@ def main():
     ap.add_argument("--oracle-rows", type=int, default=0)
     args = ap.parse_args()
     be = api.Backend(devices=tuple(range(args.devices)))
-    sk, skr, blob = api.client_keygen(N, 0x48455244)
+    sk, skr, blob = cs.keygen(N, 0x48455244)
     be.load_key_mem("s", blob)
     orc = None
     if args.oracle_rows:
@@ -115,7 +116,7 @@ def main():
         s3 = be.eval_circuit_rows("s", stages[2], np.concatenate([s2, s1, abd[:, 16:]], axis=1))
         dt = time.perf_counter() - t0
         sm = (a + b) % 256
-        good = bool(np.array_equal(cm.unpack_words(api.client_decrypt_bits(N, sk, s3)).reshape(r), np.where(sm < d, sm, d)))
+        good = bool(np.array_equal(cm.unpack_words(cs.decrypt_bits(N, sk, s3)).reshape(r), np.where(sm < d, sm, d)))
         ok &= good
         print(json.dumps({"config": "configs[4] add->compare->select (3 stages, host round trip between stages)", "rows": r,
                           "boot_gates_per_row": gates, "seconds": dt, "rows_per_s": r / dt, "gates_per_s": r * gates / dt,
@@ -125,7 +126,7 @@ def main():
         t0 = time.perf_counter()
         out = be.eval_pipeline_rows("s", chain, abd)
         dt = time.perf_counter() - t0
-        good = bool(np.array_equal(cm.unpack_words(api.client_decrypt_bits(N, sk, out)).reshape(r), np.where(sm < d, sm, d)))
+        good = bool(np.array_equal(cm.unpack_words(cs.decrypt_bits(N, sk, out)).reshape(r), np.where(sm < d, sm, d)))
         ok &= good
         print(json.dumps({"config": "configs[4] add->compare->select (3 stages, intermediate rows resident on the device)", "rows": r,
                           "boot_gates_per_row": gates, "seconds": dt, "rows_per_s": r / dt, "gates_per_s": r * gates / dt,
@@ -136,14 +137,14 @@ def main():
         pts = []
         while B <= args.sweep_max:
             a = rng.integers(0, 2, B).astype(np.uint8); b = rng.integers(0, 2, B).astype(np.uint8)
-            ca = api.client_encrypt_bits(N, sk, a, seed=2, first=0); cb = api.client_encrypt_bits(N, sk, b, seed=2, first=1 << 24)
+            ca = cs.encrypt_bits(N, sk, a, seed=2, first=0); cb = cs.encrypt_bits(N, sk, b, seed=2, first=1 << 24)
             be.eval_gate_batch("s", "NAND", ca, cb)
             be.reset_stats()
             t0 = time.perf_counter()
             out = be.eval_gate_batch("s", "NAND", ca, cb)
             dt = time.perf_counter() - t0
             st = be.stats()
-            good = bool(np.array_equal(api.client_decrypt_bits(N, sk, out), 1 - (a & b)))
+            good = bool(np.array_equal(cs.decrypt_bits(N, sk, out), 1 - (a & b)))
             ok &= good
             pts.append({"batch": B, "gates_per_s_wall": B / dt, "gates_per_s_kernels": B / ((st["blind_rotate_ms"] + st["keyswitch_ms"]) * 1e-3),
                         "ms_wall": dt * 1e3, "ok": good})
