@@ -275,6 +275,7 @@ def run_ours(args, rank, world, local_rank):
 
 
 def cpu_baseline(be, sk, args):
+    import clientsim as cs
     """oracle (port of OpenFHE binfhe EvalBinGate) on the box's host cores, bounded sample; also the parity check"""
     from herdsman_b200 import api
     from oracle import pyoracle as po
