@@ -19,7 +19,7 @@ import numpy as np
 from .circuit import Circuit, herdb_circuit, herdb_circuit_info, herdb_schedule_info
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libherdb.so")
+LIB_PATH = os.environ.get("HERDB_LIB") or os.path.join(_HERE, "libherdb.so")      # HERDB_LIB: an A/B build of the same library
 _lib = None
 
 N_STD128 = 512
@@ -33,6 +33,7 @@ EXPORTS = [
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_pipeline_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_circuit_schedule", "herdb_circuit_eval_plain", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_task_threads", "herdb_key_blob_size", "herdb_loaded_keys", "herdb_partition_count", "herdb_eval_gate_batch_dev_shape",
+    "herdb_measure_l2_bandwidth",
 ]
 
 
@@ -96,6 +97,7 @@ def lib():
         L.herdb_get_stream.argtypes = [vp, ci, C.POINTER(vp)]
         L.herdb_reset_stats.argtypes = [vp]
         L.herdb_measure_int_peak.argtypes = [vp, ci] + [C.POINTER(C.c_double)] * 5
+        L.herdb_measure_l2_bandwidth.argtypes = [vp, ci, C.POINTER(C.c_double)]
         L.herdb_task_threads.argtypes = [vp]
         L.herdb_key_blob_size.argtypes = [u32]; L.herdb_key_blob_size.restype = sz
         L.herdb_loaded_keys.argtypes = [vp]
@@ -308,6 +310,11 @@ class Backend:
         v = [C.c_double() for _ in range(5)]
         self._check(self.L.herdb_measure_int_peak(self.h, device, *[C.byref(x) for x in v]))
         return dict(zip(["imad_tops", "iadd3_tops", "imadhi_tops", "imadwide_tops", "shoup_mix_mul_tops"], [x.value for x in v]))
+
+    def measure_l2_bandwidth(self, device=0):
+        v = C.c_double()
+        self._check(self.L.herdb_measure_l2_bandwidth(self.h, device, C.byref(v)))
+        return v.value
 
     def wait_idle(self):
         self._check(self.L.herdb_wait_idle(self.h))

@@ -1071,6 +1071,32 @@ extern "C" int herdb_measure_int_peak(herdb_ctx* ctx, int device, double* imad, 
     return HERDB_OK;
 }
 
+extern "C" int herdb_measure_l2_bandwidth(herdb_ctx* ctx, int device, double* gbs) {
+    if (!ctx || !gbs || device < 0 || device >= (int)ctx->devs.size()) return HERDB_ERR_ARG;
+    Device& d = *ctx->devs[device];
+    std::lock_guard<std::mutex> l(d.mu);
+    CU(cudaSetDevice(d.id));
+    const size_t bytes = (size_t)32 << 20;                           // well inside the 126 MB L2
+    const int reps = 64;
+    void* buf = nullptr; u32* out = nullptr;
+    CU(cudaMalloc(&buf, bytes)); CU(cudaMalloc((void**)&out, 4));
+    CU(cudaMemsetAsync(buf, 1, bytes, d.stream));
+    cudaEvent_t a, b; CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep) {
+        CU(cudaEventRecord(a, d.stream));
+        CU(launch_l2_read(buf, bytes, reps, out, d.sm_count, d.stream));
+        CU(cudaEventRecord(b, d.stream));
+        CU(cudaStreamSynchronize(d.stream));
+        float ms; CU(cudaEventElapsedTime(&ms, a, b));
+        if (rep) best = std::min(best, ms);
+        d.stats.kernel_launches += 1;
+    }
+    *gbs = (double)bytes * reps / (best * 1e-3) / 1e9;
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(buf); cudaFree(out);
+    return HERDB_OK;
+}
+
 // ================================================================================================ the task seam
 // Partition files (storage_service.cpp:19-28,99-150): rows concatenated, each row
 // [u32 length, host endian][payload].  Our payload = the row's bit-ciphertexts, dense

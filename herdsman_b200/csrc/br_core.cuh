@@ -116,7 +116,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
     static_assert(!kRing || kChunks == 1, "the ring recycles the four digit slots of four ciphertexts for the four (sign, column) pieces");
     const u32 tid = env.tid();
     const u32 lane = tid & 31, warp = tid >> 5;
-    const bool has_poly = warp < 2u * kC;                          // phase A: warp = (ciphertext, component)
+    const bool has_poly = kC != 1 || warp < 2u;                    // phase A: warp = (ciphertext, component); C = 1 leaves warps 2, 3 without one
     const u32 n = P.n;
 
     // ---- ciphertext preparation: ct1 + ct2 (2*(ct1 - ct2) for XOR_FAST / XNOR_FAST), NOT folded in
@@ -240,8 +240,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
         }
         env.sync();
         // ===== phase B: thread = kChunks chunks of 4 evaluation points: 4*(tid + q*kThreads) ..+3
-#pragma unroll 1
-        for (int q = 0; q < kChunks; ++q) {
+        auto phase_b = [&](const int q) {
             // exactness of the 64-bit sums: six digit transforms below kFwdOutMax and the two accumulator components
             // below 2Q, each times a key word below Q, stay below 2^62 (what fold62_f64 accepts)
             static_assert((6 * kFwdOutMax + 2 * 2ull * kQ) < ((1ull << 62) / kQ), "key MAC fits 62 bits");
@@ -319,6 +318,11 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
                     *reinterpret_cast<V4*>(&S.acc[c][jo][phys_b]) = av;
                 }
             }
+        };
+        if constexpr (kChunks == 1) phase_b(0);
+        else {
+#pragma unroll 1
+            for (int q = 0; q < kChunks; ++q) phase_b(q);
         }
         env.sync();
     }

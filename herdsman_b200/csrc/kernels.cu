@@ -228,6 +228,19 @@ __global__ void __launch_bounds__(256) int_peak_kernel(u32* out, u32 seed, int i
     out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 
+// L2 read bandwidth: every CTA streams the same `words`-word buffer (sized to stay resident in L2) `reps` times with
+// 128-bit loads.  The roof the key switch is held against: its 2.1 MB of key rows per job are served by L2.
+__global__ void __launch_bounds__(256) l2_read_kernel(const uint4* __restrict__ buf, size_t vecs, int reps, u32* out) {
+    u32 acc = 0;
+    for (int r = 0; r < reps; ++r)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < vecs; i += (size_t)gridDim.x * blockDim.x) {
+            uint4 v;
+            asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(buf + i));
+            acc += v.x ^ v.y ^ v.z ^ v.w;
+        }
+    if (acc == 0x12345678u) out[0] = acc;
+}
+
 // ------------------------------------------------------------------------------------------------
 // launchers (plain C++ signatures so backend.cpp does not need nvcc)
 template <int C>
@@ -290,6 +303,10 @@ cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 pol
 }
 cudaError_t launch_ksk_relayout(const u16* in, u16* out, u32 n, u32 stride, size_t rows, int sm_count, cudaStream_t stream) {
     ksk_relayout_kernel<<<sm_count * 8, 256, 0, stream>>>(in, out, n, stride, rows);
+    return cudaGetLastError();
+}
+cudaError_t launch_l2_read(const void* buf, size_t bytes, int reps, u32* out, int sm_count, cudaStream_t stream) {
+    l2_read_kernel<<<sm_count * 8, 256, 0, stream>>>(static_cast<const uint4*>(buf), bytes / 16, reps, out);
     return cudaGetLastError();
 }
 cudaError_t launch_int_peak(int mode, u32* out, int blocks, int iters, cudaStream_t stream) {

@@ -267,6 +267,9 @@ int herdb_reset_stats(herdb_ctx* ctx);
 /* raw integer-pipe peak microbenchmark (IMAD / IADD3 / IMAD.HI / IMAD.WIDE), Tops/s */
 int herdb_measure_int_peak(herdb_ctx* ctx, int device, double* imad_tops, double* iadd3_tops,
                            double* imadhi_tops, double* imadwide_tops, double* mixed_tops);
+/* L2 read bandwidth (GB/s): all CTAs streaming one 32 MiB buffer with 128-bit loads; the roof of keyswitch_kernel,
+ * whose key rows are served by L2 */
+int herdb_measure_l2_bandwidth(herdb_ctx* ctx, int device, double* gbs);
 
 #ifdef __cplusplus
 }
