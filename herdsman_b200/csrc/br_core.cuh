@@ -133,11 +133,7 @@ HERDB_HD void blind_rotate_group(Env& env, const BrParams& P, BrSmem<kC>& S, u32
     }
     // lane twiddles -> smem (once per group; 2 x 8 KB)
     // (the forward table is stored with CEILING Shoup companions, w' + 1: odd words; centred butterflies, ntt_core.cuh)
-#if defined(HERDB_FWD_LAZY2Q)
-    for (u32 w = tid; w < kLaneTwWords; w += kThreads) { S.itw[w] = P.itw1[w]; S.ftw[w] = P.ftw2[w]; }
-#else
     for (u32 w = tid; w < kLaneTwWords; w += kThreads) { S.itw[w] = P.itw1[w]; S.ftw[w] = P.ftw2[w] + (w & 1u); }
-#endif
     env.sync();
     // ---- BootstrapGateCore: acc = (0, NTT(m)), m[2j] = +-(Q/8+1) depending on (b - j) in [q1, q2)
     if (has_poly) {

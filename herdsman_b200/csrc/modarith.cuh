@@ -77,10 +77,6 @@ static_assert(cmulmod(kBGInv3, cmulmod(cmulmod(kBG, kBG), kBG)) == 1, "B^-3");
 static_assert(HERDB_DIGITS_G == 4, "top-digit elimination is written for 4 gadget digits");
 constexpr u32 kDGT = HERDB_DIGITS_G - 1;   // digit polynomials actually transformed per accumulator component
 
-// 2^31 mod Q and its Shoup companion: folds the high part of a 62-bit value
-constexpr u32 kR31 = (u32)((1ull << 31) % kQ);
-constexpr u32 kR31s = cshoup(kR31);
-
 // Stages whose twiddle depends only on the register index (not on the lane) read their
 // (w, w') pairs from constant memory: the operand folds into IMAD/IMAD.HI as c[bank][imm].
 struct UniformTw { u32 v[32][2]; };
@@ -138,20 +134,15 @@ HERDB_HD u32 csub(u32 x, u32 m) { return umin32(x, x - m); }
 // any x < 2^32 -> canonical residue in [0, Q): x - (x>>27)*Q lands in [0, 2Q) because
 // x - (x>>27)*Q = (x mod 2^27) + 2047*(x>>27) < 2^27 + 2047*31 < 2Q
 HERDB_HD u32 canon32(u32 x) { return csub(x - (x >> 27) * kQ, kQ); }
-// any x < 2^62 -> residue < 2Q + 2^31 < 2^32 (not canonical)
-HERDB_HD u32 fold62(u64 x) {
-    u32 hi = (u32)(x >> 31), lo = (u32)x & 0x7FFFFFFFu;
-    return mul_shoup_lazy(kR31, kR31s, hi) + lo;
-}
-// The same fold with the quotient taken on the FP64 pipe, which is otherwise idle (DFMA issues beside IMAD on
-// B200: profiles/r01m_fp64_microbench.txt).  For x < 2^62 the register pair {lo = (x >> 11) mod 2^32,
+// Fold of a 62-bit sum with the quotient taken on the FP64 pipe, which is otherwise idle (DFMA issues beside IMAD on
+// B200: profiles/round1/r01m_fp64_microbench.txt).  For x < 2^62 the register pair {lo = (x >> 11) mod 2^32,
 // hi = 0x43300000 | (x >> 43)} read as a double is exactly 2^52 + y, y = floor(x / 2^11) < 2^51.  With the
 // integer ci = round(2^63 / Q) (37 bits), M = ci / 2^52 and C = 1.5 * 2^52 - ci - 1 (both exact doubles)
 //   fma(pair, M, C) = 1.5 * 2^52 + y * ci / 2^52 - 1, rounded once to an integer: its low word is q - 1
 //   (mod 2^32) with |q - x/Q| <= 0.5 (rounding) + 0.25 (ci) + 2^-16 (the 11 dropped bits), so
 //   r = lo32(x) - (q - 1) * Q (mod 2^32) = x - q * Q + Q exactly, in (0.2499 Q, 1.7501 Q).
 // Two shifts, one DFMA and one IMAD replace shift + mask + IMAD.HI + 2 IMAD + add; the residue class is exact,
-// only the representative differs from fold62's.  fold62_f64(x, a) = r + a for an addend a < 2^30.
+// only the representative differs from a Shoup fold's.  fold62_f64(x, a) = r + a for an addend a < 2^30.
 HERDB_HD double f64_words(u32 hi, u32 lo) {
 #if defined(__CUDA_ARCH__)
     return __hiloint2double((int)hi, (int)lo);

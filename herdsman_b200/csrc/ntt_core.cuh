@@ -62,38 +62,6 @@ HERDB_HD void fwd_pass1(u32 (&x)[32]) {           // strided layout, stages 0..4
         }
     }
 }
-// Forward pass 1 for a signed-digit polynomial given as RAW unsigned digits u = r + 64 in [0,127]
-// (true coefficient r = u - 64, i.e. u + C with C = Q - 64 as a residue).  Stage 0 has a single
-// twiddle W1, so the offset is absorbed into its two add constants:
-//   X' = (u_x + C) + W1*(u_y + C) = u_x + W1*u_y + K1,   K1 = (C + W1*C) mod Q
-//   Y' = (u_x + C) - W1*(u_y + C) = u_x - W1*u_y + K2,   K2 = ((C - W1*C) mod Q) + 2Q
-// Outputs of stage 0 are < 3Q + 127; the remaining stages are the generic lazy ones.
-constexpr u32 kDigC = kQ - 64;
-constexpr u32 kDigCw = cmulmod(ctw_fwd(1), kDigC);
-constexpr u32 kDigK1 = (kDigC + kDigCw) % kQ;
-constexpr u32 kDigK2 = (kDigC + kQ - kDigCw) % kQ + kQ2;
-HERDB_HD void fwd_pass1_digits(u32 (&x)[32]) {
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[k + 16]);
-        u32 u = x[k];
-        x[k] = u + v + kDigK1;
-        x[k + 16] = u - v + kDigK2;
-    }
-#pragma unroll
-    for (int s = 1; s < 5; ++s) {
-        const int h = 16 >> s;
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            if (k & h) continue;
-            const int idx = (1 << s) + k / (2 * h);
-            u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[k + h]);
-            u32 u = x[k];
-            x[k] = u + v;
-            x[k + h] = u - v + kQ2;
-        }
-    }
-}
 HERDB_HD void fwd_pass2(u32 (&x)[32], const u32 (&tw)[62]) {   // contiguous layout, stages 5..9
     int off = 0;
 #pragma unroll
@@ -132,38 +100,10 @@ HERDB_HD void fwd_pass2_stream(u32 (&x)[32], const u32* lane_tw, u32 lane) {
     }
 }
 
-// M digit polynomials of the same accumulator component transformed together by one warp: M independent
+// M digit polynomials of the same accumulator component are transformed together by one warp: M independent
 // butterflies per twiddle give the scheduler M times the instruction-level parallelism (a warp shares its
 // scheduler with only one other warp) and every streamed twiddle pair is loaded once for the M of them.
-template <int M>
-HERDB_HD void fwd_pass1_digits_multi(u32 (&x)[M][32]) {
-#pragma unroll
-    for (int k = 0; k < 16; ++k)
-#pragma unroll
-        for (int m = 0; m < M; ++m) {
-            u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[m][k + 16]);
-            u32 u = x[m][k];
-            x[m][k] = u + v + kDigK1;
-            x[m][k + 16] = u - v + kDigK2;
-        }
-#pragma unroll
-    for (int s = 1; s < 5; ++s) {
-        const int h = 16 >> s;
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            if (k & h) continue;
-            const int idx = (1 << s) + k / (2 * h);
-#pragma unroll
-            for (int m = 0; m < M; ++m) {
-                u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[m][k + h]);
-                u32 u = x[m][k];
-                x[m][k] = u + v;
-                x[m][k + h] = u - v + kQ2;
-            }
-        }
-    }
-}
-// The same with digit l given IN PLACE: x[l][k] = (r_l + 64) * 2^(7l), the 7-bit field of the decomposed value
+// Digit l is given IN PLACE: x[l][k] = (r_l + 64) * 2^(7l), the 7-bit field of the decomposed value
 // masked but not shifted down.  The transform is linear, so the warp computes 2^(7l) * NTT(r_l); the factor
 // 2^(-7l) sits in the folded key rows (fold_top_digit).  Saves the shift of every digit extraction; the offset
 // 64 * 2^(7l) goes into the add constants of stage 0 as before.  Inputs < 2^21, outputs < 3Q + 2^21 + 8Q.
@@ -202,13 +142,8 @@ HERDB_HD void fwd_pass1_fields_multi(u32 (&x)[M][32]) {
             const u32 k2 = m == 0 ? kDigF2_0 : m == 1 ? kDigF2_1 : kDigF2_2;
             u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[m][k + 16]);
             u32 u = x[m][k];
-#if defined(HERDB_FWD_LAZY2Q)
-            x[m][k] = u + v + k1;
-            x[m][k + 16] = u - v + k2;
-#else
             x[m][k] = u + v + (k1 + kFwdStart - kQ);          // v - Q in [-Q, Q): values in [10 Q, 13 Q + 2^21)
             x[m][k + 16] = u - v + (k2 - kQ2 + kFwdStart + kQ);
-#endif
         }
 #pragma unroll
     for (int s = 1; s < 5; ++s) {
@@ -219,14 +154,7 @@ HERDB_HD void fwd_pass1_fields_multi(u32 (&x)[M][32]) {
             const int idx = (1 << s) + k / (2 * h);
 #pragma unroll
             for (int m = 0; m < M; ++m) {
-#if defined(HERDB_FWD_LAZY2Q)
-                u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[m][k + h]);
-                u32 u = x[m][k];
-                x[m][k] = u + v;
-                x[m][k + h] = u - v + kQ2;
-#else
                 bfly_fwd_centred(x[m][k], x[m][k + h], HERDB_TWFU(idx, 0), HERDB_TWFU(idx, 1));
-#endif
             }
         }
     }
@@ -246,14 +174,7 @@ HERDB_HD void fwd_pass2_stream_multi(u32 (&x)[M][32], const u32* lane_tw, u32 la
             const u32 w = tp[0], wp = tp[1];
 #pragma unroll
             for (int m = 0; m < M; ++m) {
-#if defined(HERDB_FWD_LAZY2Q)
-                u32 v = mul_shoup_lazy(w, wp, x[m][e + t]);
-                u32 u = x[m][e];
-                x[m][e] = u + v;
-                x[m][e + t] = u - v + kQ2;
-#else
                 bfly_fwd_centred(x[m][e], x[m][e + t], w, wp);
-#endif
             }
         }
         off += 16 / t;

@@ -1,9 +1,84 @@
-// tools/experimental_ntt.cuh -- NTT butterfly variants that were measured on B200 and NOT adopted by the
-// product kernel (DESIGN.md "What was tried"): quotients on the FP64 pipe (two forms), a hybrid
-// FP64/Shoup forward pass, and two polynomials per warp in lock-step.  Used only by tools/ntt_bench.cu and
-// tools/microbench{4,5}.cu; kept so the measurements in profiles/ can be reproduced.
+// tools/microbench/experimental_ntt.cuh -- NTT butterfly variants that were measured on B200 and NOT adopted by
+// the product kernel (DESIGN.md "What was tried"): quotients on the FP64 pipe (two forms), a hybrid FP64/Shoup
+// forward pass, two polynomials per warp in lock-step, and the earlier forms of the product code the centred
+// butterflies and the FP64 folds replaced ([0, 2Q) forward pass 1 on raw digits, the Shoup fold of a 62-bit sum).
+// Used only by the micro-benchmarks in this directory; kept so the measurements in profiles/round1/r01* can be reproduced.
 #pragma once
-#include "../herdsman_b200/csrc/ntt_core.cuh"
+#include "../../herdsman_b200/csrc/ntt_core.cuh"
+namespace herdb {
+// 2^31 mod Q and its Shoup companion: folds the high part of a 62-bit value
+constexpr u32 kR31 = (u32)((1ull << 31) % kQ);
+constexpr u32 kR31s = cshoup(kR31);
+
+// any x < 2^62 -> residue < 2Q + 2^31 < 2^32 (not canonical)
+HERDB_HD u32 fold62(u64 x) {
+    u32 hi = (u32)(x >> 31), lo = (u32)x & 0x7FFFFFFFu;
+    return mul_shoup_lazy(kR31, kR31s, hi) + lo;
+}
+// Forward pass 1 for a signed-digit polynomial given as RAW unsigned digits u = r + 64 in [0,127]
+// (true coefficient r = u - 64, i.e. u + C with C = Q - 64 as a residue).  Stage 0 has a single
+// twiddle W1, so the offset is absorbed into its two add constants:
+//   X' = (u_x + C) + W1*(u_y + C) = u_x + W1*u_y + K1,   K1 = (C + W1*C) mod Q
+//   Y' = (u_x + C) - W1*(u_y + C) = u_x - W1*u_y + K2,   K2 = ((C - W1*C) mod Q) + 2Q
+// Outputs of stage 0 are < 3Q + 127; the remaining stages are the generic lazy ones.
+constexpr u32 kDigC = kQ - 64;
+constexpr u32 kDigCw = cmulmod(ctw_fwd(1), kDigC);
+constexpr u32 kDigK1 = (kDigC + kDigCw) % kQ;
+constexpr u32 kDigK2 = (kDigC + kQ - kDigCw) % kQ + kQ2;
+HERDB_HD void fwd_pass1_digits(u32 (&x)[32]) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[k + 16]);
+        u32 u = x[k];
+        x[k] = u + v + kDigK1;
+        x[k + 16] = u - v + kDigK2;
+    }
+#pragma unroll
+    for (int s = 1; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+            u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[k + h]);
+            u32 u = x[k];
+            x[k] = u + v;
+            x[k + h] = u - v + kQ2;
+        }
+    }
+}
+// M digit polynomials of the same accumulator component transformed together by one warp: M independent
+// butterflies per twiddle give the scheduler M times the instruction-level parallelism (a warp shares its
+// scheduler with only one other warp) and every streamed twiddle pair is loaded once for the M of them.
+template <int M>
+HERDB_HD void fwd_pass1_digits_multi(u32 (&x)[M][32]) {
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            u32 v = mul_shoup_lazy(HERDB_TWF(1, 0), HERDB_TWF(1, 1), x[m][k + 16]);
+            u32 u = x[m][k];
+            x[m][k] = u + v + kDigK1;
+            x[m][k + 16] = u - v + kDigK2;
+        }
+#pragma unroll
+    for (int s = 1; s < 5; ++s) {
+        const int h = 16 >> s;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            if (k & h) continue;
+            const int idx = (1 << s) + k / (2 * h);
+#pragma unroll
+            for (int m = 0; m < M; ++m) {
+                u32 v = mul_shoup_lazy(HERDB_TWF(idx, 0), HERDB_TWF(idx, 1), x[m][k + h]);
+                u32 u = x[m][k];
+                x[m][k] = u + v;
+                x[m][k + h] = u - v + kQ2;
+            }
+        }
+    }
+}
+}  // namespace herdb
 // ================================================================================================
 // FP64-assisted modular multiplication.  On B200 IMAD.HI (and IMAD.WIDE) cost two issue slots of the
 // FMA pipe, so a Shoup product (IMAD.HI, IMAD, IMAD) occupies it for 4 slots.  The quotient can be

@@ -7,7 +7,7 @@
 #include <cstdio>
 #include <vector>
 #include <cuda_runtime.h>
-#include "../herdsman_b200/csrc/ntt_core.cuh"
+#include "experimental_ntt.cuh"
 using namespace herdb;
 
 struct Smem {
