@@ -60,18 +60,18 @@ int grow_pinned(herdb_ctx* ctx, void** p, size_t* cap, size_t need) {
 
 // ---------------------------------------------------------------------------------------------- kernel timing
 // CUDA events around the two hot kernels, on the launching stream; summed into herdb_stats once complete
-int timed_begin(herdb_ctx* ctx, Device& d, int kind) {
+int timed_begin(herdb_ctx* ctx, Device& d, int kind, cudaStream_t stream) {
     Device::Timed t{}; t.kind = kind;
     for (cudaEvent_t* e : {&t.a, &t.b}) {
         if (!d.free_events.empty()) { *e = d.free_events.back(); d.free_events.pop_back(); }
         else CU(cudaEventCreate(e));
     }
     d.timed.push_back(t);
-    CU(cudaEventRecord(t.a, d.stream));
+    CU(cudaEventRecord(t.a, stream));
     return HERDB_OK;
 }
-int timed_end(herdb_ctx* ctx, Device& d) {
-    CU(cudaEventRecord(d.timed.back().b, d.stream));
+int timed_end(herdb_ctx* ctx, Device& d, cudaStream_t stream) {
+    CU(cudaEventRecord(d.timed.back().b, stream));
     return HERDB_OK;
 }
 void account(Device& d, const Device::Timed& t) {
@@ -82,13 +82,15 @@ void account(Device& d, const Device::Timed& t) {
     }
     d.free_events.push_back(t.a); d.free_events.push_back(t.b);
 }
-void drain_ready(Device& d) {                        // intervals that have completed, oldest first (no waiting)
-    while (!d.timed.empty() && cudaEventQuery(d.timed.front().b) == cudaSuccess) { account(d, d.timed.front()); d.timed.pop_front(); }
+void drain_ready(Device& d) {                        // intervals that have completed (no waiting); several streams feed the list
+    for (auto it = d.timed.begin(); it != d.timed.end();) {
+        if (cudaEventQuery(it->b) == cudaSuccess) { account(d, *it); it = d.timed.erase(it); } else ++it;
+    }
     cudaGetLastError();                              // cudaErrorNotReady is not an error
 }
-int drain(herdb_ctx* ctx, Device& d) {
+int drain(herdb_ctx* ctx, Device& d) {              // the device's own kernel stream (single-stream entry points)
     CU(cudaStreamSynchronize(d.stream));
-    while (!d.timed.empty()) { account(d, d.timed.front()); d.timed.pop_front(); }
+    drain_ready(d);
     return HERDB_OK;
 }
 
@@ -99,26 +101,27 @@ const DeviceKey* find_key(Device& d, const char* session) {
 
 // ---------------------------------------------------------------------------------------------- one level, one circuit
 // one circuit level (or a single-gate pseudo level): blind rotation then key switch, `rows` rows
-int run_level(herdb_ctx* ctx, Device& d, const DeviceKey& key, const GateDesc* d_gates, u32 n_gates,
+struct Exec { cudaStream_t stream; u16* slots; u16* ext; };     // where a level runs: kernel stream + scratch
+int run_level(herdb_ctx* ctx, Device& d, const Exec& ex, const DeviceKey& key, const GateDesc* d_gates, u32 n_gates,
               const Pool pools[4], u32 rows, u32* d_trace = nullptr, u32 steps = UINT32_MAX, int shape = 0) {
     const u32 jobs = n_gates * rows;
     if (!jobs) return HERDB_OK;
     BrParams bp{};
     bp.bsk = key.bsk; bp.mono = d.mono; bp.ftw2 = d.ftw2; bp.itw1 = d.itw1; bp.gates = d_gates;
     for (int i = 0; i < 4; ++i) bp.pools[i] = pools[i];
-    bp.ext = d.ext; bp.trace = d_trace; bp.n = key.n; bp.steps = std::min(steps, key.n); bp.rows = rows; bp.jobs = jobs;
+    bp.ext = ex.ext; bp.trace = d_trace; bp.n = key.n; bp.steps = std::min(steps, key.n); bp.rows = rows; bp.jobs = jobs;
     bp.job0 = 0; bp.job1 = jobs;
     int launches = 0;
-    int rc = timed_begin(ctx, d, 0); if (rc) return rc;
-    CU(launch_blind_rotate(bp, d.sm_count, d.stream, shape, &launches));
-    rc = timed_end(ctx, d); if (rc) return rc;
+    int rc = timed_begin(ctx, d, 0, ex.stream); if (rc) return rc;
+    CU(launch_blind_rotate(bp, d.sm_count, ex.stream, shape, &launches));
+    rc = timed_end(ctx, d, ex.stream); if (rc) return rc;
     KsParams kp{};
-    kp.ksk = key.ksk; kp.ext = d.ext; kp.gates = d_gates;
+    kp.ksk = key.ksk; kp.ext = ex.ext; kp.gates = d_gates;
     for (int i = 0; i < 4; ++i) kp.pools[i] = pools[i];
     kp.ks_stride = key.ks_stride; kp.n = key.n; kp.rows = rows; kp.jobs = jobs;
-    rc = timed_begin(ctx, d, 1); if (rc) return rc;
-    CU(launch_keyswitch(kp, d.sm_count, d.stream));
-    rc = timed_end(ctx, d); if (rc) return rc;
+    rc = timed_begin(ctx, d, 1, ex.stream); if (rc) return rc;
+    CU(launch_keyswitch(kp, d.sm_count, ex.stream));
+    rc = timed_end(ctx, d, ex.stream); if (rc) return rc;
     d.stats.kernel_launches += (uint64_t)launches + 1;
     d.stats.gates_bootstrapped += jobs;
     return HERDB_OK;
@@ -130,34 +133,34 @@ size_t scratch_per_row(const CompiledCircuit& cc, u32 n) {
 
 // all levels of one compiled circuit over `rows` rows that are resident on the device; the gate and output
 // tables are already there (d_gates = all levels back to back).  Asynchronous: kernels are queued on d.stream.
-int issue_circuit(herdb_ctx* ctx, Device& d, const DeviceKey& key, const CompiledCircuit& cc, const GateDesc* d_gates,
+int issue_circuit(herdb_ctx* ctx, Device& d, const Exec& ex, const DeviceKey& key, const CompiledCircuit& cc, const GateDesc* d_gates,
                   const OutDesc* d_outs, Pool in, Pool out, bool out_framed, u32 rows) {
     if (!rows) return HERDB_OK;
     const u32 w = key.n + 1;
     Pool pools[4] = {};
     pools[kPoolIn] = in;
-    pools[kPoolSlots] = Pool{d.slots, cc.slots * w, 0};
+    pools[kPoolSlots] = Pool{ex.slots, cc.slots * w, 0};
     pools[kPoolOut] = out;
     size_t off = 0;
     for (auto& L : cc.levels) {
-        int rc = run_level(ctx, d, key, d_gates + off, (u32)L.size(), pools, rows); if (rc) return rc;
+        int rc = run_level(ctx, d, ex, key, d_gates + off, (u32)L.size(), pools, rows); if (rc) return rc;
         off += L.size();
     }
     GatherParams gp{};
     gp.outs = d_outs; for (int i = 0; i < 4; ++i) gp.pools[i] = pools[i];
     gp.n = key.n; gp.rows = rows; gp.out_bits = cc.out_bits;
     gp.framed = out_framed ? 1u : 0u; gp.frame_len = cc.out_bits * w * 2;
-    CU(launch_gather_outputs(gp, d.sm_count, d.stream));
+    CU(launch_gather_outputs(gp, d.sm_count, ex.stream));
     d.stats.kernel_launches += 1;
     return HERDB_OK;
 }
 
-int ensure_scratch(herdb_ctx* ctx, Device& d, const CompiledCircuit& cc, u32 n, size_t rows) {
-    int rc = grow(ctx, (void**)&d.slots, &d.slots_bytes, std::max<size_t>(16, rows * cc.slots * (n + 1) * 2)); if (rc) return rc;
-    return grow(ctx, (void**)&d.ext, &d.ext_bytes, std::max<size_t>(16, rows * cc.max_level_width * kExtStride * 2));
+int ensure_scratch(herdb_ctx* ctx, u16** slots, size_t* slots_bytes, u16** ext, size_t* ext_bytes, const CompiledCircuit& cc, u32 n, size_t rows) {
+    int rc = grow(ctx, (void**)slots, slots_bytes, std::max<size_t>(16, rows * cc.slots * (n + 1) * 2)); if (rc) return rc;
+    return grow(ctx, (void**)ext, ext_bytes, std::max<size_t>(16, rows * cc.max_level_width * kExtStride * 2));
 }
 
-int upload_tables(herdb_ctx* ctx, Device& d, const std::vector<const CompiledCircuit*>& stages, GateDesc** gates, size_t* gates_cap,
+int upload_tables(herdb_ctx* ctx, cudaStream_t stream, const std::vector<const CompiledCircuit*>& stages, GateDesc** gates, size_t* gates_cap,
                   OutDesc** outs, size_t* outs_cap, std::vector<size_t>& gate_off, std::vector<size_t>& out_off) {
     std::vector<GateDesc> flat; std::vector<OutDesc> oflat;
     for (const CompiledCircuit* cc : stages) {
@@ -167,9 +170,9 @@ int upload_tables(herdb_ctx* ctx, Device& d, const std::vector<const CompiledCir
     }
     int rc = grow(ctx, (void**)gates, gates_cap, std::max<size_t>(1, flat.size()) * sizeof(GateDesc)); if (rc) return rc;
     rc = grow(ctx, (void**)outs, outs_cap, std::max<size_t>(1, oflat.size()) * sizeof(OutDesc)); if (rc) return rc;
-    if (!flat.empty()) CU(cudaMemcpyAsync(*gates, flat.data(), flat.size() * sizeof(GateDesc), cudaMemcpyHostToDevice, d.stream));
-    if (!oflat.empty()) CU(cudaMemcpyAsync(*outs, oflat.data(), oflat.size() * sizeof(OutDesc), cudaMemcpyHostToDevice, d.stream));
-    CU(cudaStreamSynchronize(d.stream));             // `flat` / `oflat` are pageable host memory
+    if (!flat.empty()) CU(cudaMemcpyAsync(*gates, flat.data(), flat.size() * sizeof(GateDesc), cudaMemcpyHostToDevice, stream));
+    if (!oflat.empty()) CU(cudaMemcpyAsync(*outs, oflat.data(), oflat.size() * sizeof(OutDesc), cudaMemcpyHostToDevice, stream));
+    CU(cudaStreamSynchronize(stream));               // `flat` / `oflat` are pageable host memory
     return HERDB_OK;
 }
 
@@ -425,16 +428,17 @@ int make_plan(herdb_ctx* ctx, const herdb_circuit* const* circuits, size_t n_sta
         io_row = std::max(io_row, (size_t)std::max(plan.stages[k].in_bits, plan.stages[k].out_bits) * w * 2 + 4);
         widest = std::max(widest, plan.stages[k].max_level_width);
     }
-    size_t chunk = std::max<size_t>(1, std::min(ctx->mem_budget / scratch, ctx->io_budget / io_row));
+    size_t chunk = std::max<size_t>(1, std::min(ctx->mem_budget / (2 * scratch), ctx->io_budget / io_row));   // two chunks in flight
     chunk = std::min<size_t>(chunk, (size_t)0x7FFFFFFF / widest);
     chunk = std::min(chunk, std::max<size_t>(1, rows_dev));
-    const size_t nch = (std::max<size_t>(1, rows_dev) + chunk - 1) / chunk;
+    size_t nch = (std::max<size_t>(1, rows_dev) + chunk - 1) / chunk;
+    if (nch < 2 && rows_dev >= 2) nch = 2;                                                  // two chunks: both kernel streams of a lane have work
     chunk = (std::max<size_t>(1, rows_dev) + nch - 1) / nch;                                // equal chunks: no short last one
     SchedHint hint; hint.rows = chunk; hint.wave = ctx->devs.empty() ? 0 : (u32)ctx->devs[0]->sm_count * kBrCtsPerCta;
     for (size_t k = 0; k < n_stages && n_rows; ++k) {
         std::string err;
         CompiledCircuit cc;
-        if (compile_circuit(circuits[k], cc, err, hint) == HERDB_OK && scratch_per_row(cc, n) * chunk <= std::max(ctx->mem_budget, scratch_per_row(cc, n)))
+        if (compile_circuit(circuits[k], cc, err, hint) == HERDB_OK && 2 * scratch_per_row(cc, n) * chunk <= std::max(ctx->mem_budget, 2 * scratch_per_row(cc, n)))
             plan.stages[k] = std::move(cc);
     }
     plan.chunk_rows = chunk;
@@ -444,20 +448,20 @@ int make_plan(herdb_ctx* ctx, const herdb_circuit* const* circuits, size_t n_sta
 Lane* acquire_lane(Device& d) {                      // d.mu held
     for (Lane* L : d.lanes) if (!L->busy) { L->busy = true; return L; }
     Lane* L = new Lane; L->busy = true;
-    for (int b = 0; b < 2; ++b) {
-        cudaEventCreateWithFlags(&L->ev_in[b], cudaEventDisableTiming);
-        cudaEventCreateWithFlags(&L->ev_done[b], cudaEventDisableTiming);
-        cudaEventCreateWithFlags(&L->ev_out[b], cudaEventDisableTiming);
+    for (LaneHalf& h : L->half) {
+        cudaStreamCreateWithFlags(&h.stream, cudaStreamNonBlocking);
+        for (cudaEvent_t* e : {&h.ev_in, &h.ev_done, &h.ev_out}) cudaEventCreateWithFlags(e, cudaEventDisableTiming);
     }
     d.lanes.push_back(L);
     return L;
 }
 void free_lane(Lane* L) {
-    for (int b = 0; b < 2; ++b) {
-        if (L->h_in[b]) cudaFreeHost(L->h_in[b]);
-        if (L->h_out[b]) cudaFreeHost(L->h_out[b]);
-        cudaFree(L->d_in[b]); cudaFree(L->d_out[b]); cudaFree(L->d_mid[b]);
-        for (cudaEvent_t e : {L->ev_in[b], L->ev_done[b], L->ev_out[b]}) if (e) cudaEventDestroy(e);
+    for (LaneHalf& h : L->half) {
+        if (h.stream) { cudaStreamSynchronize(h.stream); cudaStreamDestroy(h.stream); }
+        if (h.h_in) cudaFreeHost(h.h_in);
+        if (h.h_out) cudaFreeHost(h.h_out);
+        cudaFree(h.slots); cudaFree(h.ext); cudaFree(h.d_in); cudaFree(h.d_out); cudaFree(h.d_mid[0]); cudaFree(h.d_mid[1]);
+        for (cudaEvent_t e : {h.ev_in, h.ev_done, h.ev_out}) if (e) cudaEventDestroy(e);
     }
     cudaFree(L->gates); cudaFree(L->outs);
     delete L;
@@ -493,7 +497,8 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
     const size_t in_stride = in_payload + (in_framed ? 4 : 0), out_stride = out_payload + (out_framed ? 4 : 0);
     size_t mid_row = 0;
     for (size_t k = 0; k + 1 < S; ++k) mid_row = std::max(mid_row, (size_t)plan.stages[k].out_bits * w * 2);
-    const size_t chunk = std::min(plan.chunk_rows, rows);
+    // equal chunks (make_plan), at least two when there are two rows: consecutive chunks run on the lane's two kernel streams
+    const size_t chunk = std::max<size_t>(1, std::min(plan.chunk_rows, rows));
     const size_t nch = (rows + chunk - 1) / chunk;
     const bool stage_in = !(io.src_mem && io.src_pinned), stage_out = !(io.dst_mem && io.dst_pinned);
 
@@ -507,71 +512,71 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
         key = find_key(d, session);
         if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
         L = acquire_lane(d);
+        int rc = HERDB_OK;
+        for (size_t b = 0; b < std::min<size_t>(2, nch) && !rc; ++b) {
+            LaneHalf& h = L->half[b];
+            rc = grow(ctx, (void**)&h.d_in, &h.d_in_cap, std::max<size_t>(16, chunk * in_stride));
+            if (!rc) rc = grow(ctx, (void**)&h.d_out, &h.d_out_cap, std::max<size_t>(16, chunk * out_stride));
+            if (!rc && stage_in) rc = grow_pinned(ctx, &h.h_in, &h.h_in_cap, std::max<size_t>(16, chunk * in_stride));
+            if (!rc && stage_out) rc = grow_pinned(ctx, &h.h_out, &h.h_out_cap, std::max<size_t>(16, chunk * out_stride));
+            for (int m = 0; m < 2 && !rc && S > 1; ++m) rc = grow(ctx, (void**)&h.d_mid[m], &h.d_mid_cap[m], std::max<size_t>(16, chunk * mid_row));
+            for (size_t k = 0; k < S && !rc; ++k) rc = ensure_scratch(ctx, &h.slots, &h.slots_bytes, &h.ext, &h.ext_bytes, plan.stages[k], plan.n, chunk);
+        }
+        if (!rc) rc = upload_tables(ctx, L->half[0].stream, stage_ptrs, &L->gates, &L->gates_cap, &L->outs, &L->outs_cap, gate_off, out_off);
+        if (rc) { L->busy = false; return rc; }
     }
     auto release = [&](int rc) {
         std::lock_guard<std::mutex> l(d.mu);
         cudaSetDevice(d.id);
-        if (rc) { cudaStreamSynchronize(d.stream); cudaStreamSynchronize(d.copy); cudaStreamSynchronize(d.copy_out); }
+        for (LaneHalf& h : L->half) cudaStreamSynchronize(h.stream);             // nothing of this evaluation is in flight any more
+        cudaStreamSynchronize(d.copy); cudaStreamSynchronize(d.copy_out);
+        drain_ready(d);
         L->busy = false;
         return rc;
     };
-    {
-        std::lock_guard<std::mutex> l(d.mu);
-        int rc = HERDB_OK;
-        for (int b = 0; b < 2 && !rc; ++b) {
-            if (nch == 1 && b == 1) break;
-            rc = grow(ctx, (void**)&L->d_in[b], &L->d_in_cap[b], std::max<size_t>(16, chunk * in_stride));
-            if (!rc) rc = grow(ctx, (void**)&L->d_out[b], &L->d_out_cap[b], std::max<size_t>(16, chunk * out_stride));
-            if (!rc && stage_in) rc = grow_pinned(ctx, &L->h_in[b], &L->h_in_cap[b], std::max<size_t>(16, chunk * in_stride));
-            if (!rc && stage_out) rc = grow_pinned(ctx, &L->h_out[b], &L->h_out_cap[b], std::max<size_t>(16, chunk * out_stride));
-        }
-        for (int b = 0; b < 2 && !rc && S > 1; ++b) rc = grow(ctx, (void**)&L->d_mid[b], &L->d_mid_cap[b], std::max<size_t>(16, chunk * mid_row));
-        for (size_t k = 0; k < S && !rc; ++k) rc = ensure_scratch(ctx, d, plan.stages[k], plan.n, chunk);
-        if (!rc) rc = upload_tables(ctx, d, stage_ptrs, &L->gates, &L->gates_cap, &L->outs, &L->outs_cap, gate_off, out_off);
-        if (rc) { L->busy = false; return rc; }
-    }
 
     int rc = HERDB_OK;
     for (size_t c = 0; c <= nch && !rc; ++c) {
         if (c < nch) {
-            const int b = (int)(c & 1);
+            LaneHalf& h = L->half[c & 1];
             const size_t row = r0 + c * chunk, cnt = std::min(chunk, rows - c * chunk);
             const void* h_src = nullptr;
             if (in_stride) {
                 if (stage_in) {
-                    if (c >= 2 && cudaEventSynchronize(L->ev_in[b]) != cudaSuccess) { ctx->set_error("upload failed"); rc = HERDB_ERR_CUDA; break; }
+                    if (c >= 2 && cudaEventSynchronize(h.ev_in) != cudaSuccess) { ctx->set_error("upload failed"); rc = HERDB_ERR_CUDA; break; }
                     if (in_framed) {
-                        if (full_pread(io.src_fd, L->h_in[b], cnt * in_stride, (off_t)(row * in_stride)) != 0) { ctx->set_error("short read of the input partition"); rc = HERDB_ERR_IO; break; }
+                        if (full_pread(io.src_fd, h.h_in, cnt * in_stride, (off_t)(row * in_stride)) != 0) { ctx->set_error("short read of the input partition"); rc = HERDB_ERR_IO; break; }
                         for (size_t r = 0; r < cnt; ++r) {                                 // every row announces exactly the circuit's input row
-                            uint32_t len; memcpy(&len, (const uint8_t*)L->h_in[b] + r * in_stride, 4);
+                            uint32_t len; memcpy(&len, (const uint8_t*)h.h_in + r * in_stride, 4);
                             if (len != in_payload) { rc = HERDB_ERR_FORMAT; break; }
                         }
                         if (rc) { ctx->set_error("input partition: row length does not match the circuit's input columns"); break; }
-                    } else memcpy(L->h_in[b], io.src_mem + row * in_stride, cnt * in_stride);
-                    h_src = L->h_in[b];
+                    } else memcpy(h.h_in, io.src_mem + row * in_stride, cnt * in_stride);
+                    h_src = h.h_in;
                 } else h_src = io.src_mem + row * in_stride;
             }
             std::lock_guard<std::mutex> l(d.mu);
             NvtxRange chunk_range("herdb:chunk_issue");
             auto issue = [&]() -> int {
                 CU(cudaSetDevice(d.id));
-                if (c >= 2) CU(cudaStreamWaitEvent(d.copy, L->ev_done[b], 0));           // kernels of chunk c-2 have read d_in[b]
-                if (in_stride) CU(cudaMemcpyAsync(L->d_in[b], h_src, cnt * in_stride, cudaMemcpyHostToDevice, d.copy));
-                CU(cudaEventRecord(L->ev_in[b], d.copy));
-                CU(cudaStreamWaitEvent(d.stream, L->ev_in[b], 0));
-                if (c >= 2) CU(cudaStreamWaitEvent(d.stream, L->ev_out[b], 0));           // download of chunk c-2 has read d_out[b]
+                if (c >= 2) CU(cudaStreamWaitEvent(d.copy, h.ev_done, 0));               // kernels of chunk c-2 have read d_in
+                if (in_stride) CU(cudaMemcpyAsync(h.d_in, h_src, cnt * in_stride, cudaMemcpyHostToDevice, d.copy));
+                CU(cudaEventRecord(h.ev_in, d.copy));
+                CU(cudaStreamWaitEvent(h.stream, h.ev_in, 0));
+                if (c >= 2) CU(cudaStreamWaitEvent(h.stream, h.ev_out, 0));               // download of chunk c-2 has read d_out
+                const Exec ex{h.stream, h.slots, h.ext};
                 for (size_t k = 0; k < S; ++k) {
                     const CompiledCircuit& cc = plan.stages[k];
-                    Pool in = k == 0 ? Pool{L->d_in[b] + (in_framed ? 2 : 0), (u32)(in_stride / 2), 0} : Pool{L->d_mid[(k - 1) & 1], cc.in_bits * (u32)w, 0};
-                    Pool out = k + 1 == S ? Pool{L->d_out[b] + (out_framed ? 2 : 0), (u32)(out_stride / 2), 0} : Pool{L->d_mid[k & 1], cc.out_bits * (u32)w, 0};
-                    int r2 = issue_circuit(ctx, d, *key, cc, L->gates + gate_off[k], L->outs + out_off[k], in, out, k + 1 == S && out_framed, (u32)cnt);
+                    Pool in = k == 0 ? Pool{h.d_in + (in_framed ? 2 : 0), (u32)(in_stride / 2), 0} : Pool{h.d_mid[(k - 1) & 1], cc.in_bits * (u32)w, 0};
+                    Pool out = k + 1 == S ? Pool{h.d_out + (out_framed ? 2 : 0), (u32)(out_stride / 2), 0} : Pool{h.d_mid[k & 1], cc.out_bits * (u32)w, 0};
+                    int r2 = issue_circuit(ctx, d, ex, *key, cc, L->gates + gate_off[k], L->outs + out_off[k], in, out, k + 1 == S && out_framed, (u32)cnt);
                     if (r2) return r2;
                 }
-                CU(cudaEventRecord(L->ev_done[b], d.stream));
-                CU(cudaStreamWaitEvent(d.copy_out, L->ev_done[b], 0));
-                void* h_dst = stage_out ? L->h_out[b] : (void*)(io.dst_mem + row * out_stride);
-                if (out_stride) CU(cudaMemcpyAsync(h_dst, L->d_out[b], cnt * out_stride, cudaMemcpyDeviceToHost, d.copy_out));
-                CU(cudaEventRecord(L->ev_out[b], d.copy_out));
+                CU(cudaEventRecord(h.ev_done, h.stream));
+                CU(cudaStreamWaitEvent(d.copy_out, h.ev_done, 0));
+                void* h_dst = stage_out ? h.h_out : (void*)(io.dst_mem + row * out_stride);
+                if (out_stride) CU(cudaMemcpyAsync(h_dst, h.d_out, cnt * out_stride, cudaMemcpyDeviceToHost, d.copy_out));
+                CU(cudaEventRecord(h.ev_out, d.copy_out));
                 d.stats.h2d_bytes += cnt * in_stride; d.stats.d2h_bytes += cnt * out_stride;
                 return HERDB_OK;
             };
@@ -579,13 +584,13 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
             if (rc) break;
         }
         if (c >= 1) {                                                                      // chunk c-1: wait for its rows, hand them to the sink
-            const int pb = (int)((c - 1) & 1);
+            LaneHalf& h = L->half[(c - 1) & 1];
             const size_t row = r0 + (c - 1) * chunk, cnt = std::min(chunk, rows - (c - 1) * chunk);
-            if (cudaEventSynchronize(L->ev_out[pb]) != cudaSuccess) { ctx->set_error(std::string("evaluation failed: ") + cudaGetErrorString(cudaGetLastError())); rc = HERDB_ERR_CUDA; break; }
+            if (cudaEventSynchronize(h.ev_out) != cudaSuccess) { ctx->set_error(std::string("evaluation failed: ") + cudaGetErrorString(cudaGetLastError())); rc = HERDB_ERR_CUDA; break; }
             if (out_stride && stage_out) {
                 if (out_framed) {
-                    if (full_pwrite(io.dst_fd, L->h_out[pb], cnt * out_stride, (off_t)(row * out_stride)) != 0) { ctx->set_error("cannot write the output partition"); rc = HERDB_ERR_IO; break; }
-                } else memcpy(io.dst_mem + row * out_stride, L->h_out[pb], cnt * out_stride);
+                    if (full_pwrite(io.dst_fd, h.h_out, cnt * out_stride, (off_t)(row * out_stride)) != 0) { ctx->set_error("cannot write the output partition"); rc = HERDB_ERR_IO; break; }
+                } else memcpy(io.dst_mem + row * out_stride, h.h_out, cnt * out_stride);
             }
             std::lock_guard<std::mutex> l(d.mu);
             drain_ready(d);
@@ -611,13 +616,7 @@ int eval_rows_pipelined(herdb_ctx* ctx, const char* session, const EvalPlan& pla
         for (size_t di = 0; di < G; ++di) th.emplace_back(run_slice, di);
         for (auto& t : th) t.join();
     }
-    for (size_t di = 0; di < G; ++di) {                  // timing intervals of this evaluation are in the stats when the call returns
-        Device& d = *ctx->devs[di];
-        std::lock_guard<std::mutex> l(d.mu);
-        cudaSetDevice(d.id);
-        if (!rcs[di]) rcs[di] = drain(ctx, d);
-    }
-    for (int rc : rcs) if (rc) return rc;
+    for (int rc : rcs) if (rc) return rc;                // (the timing intervals of this evaluation are in the stats: release())
     return HERDB_OK;
 }
 
@@ -855,7 +854,7 @@ static int gate_batch_launch(herdb_ctx* ctx, Device& d, const DeviceKey& key, co
         pools[0] = Pool{const_cast<u16*>(d_a) + r0 * w, (u32)w, 0};
         pools[2] = Pool{const_cast<u16*>(d_b) + r0 * w, (u32)w, 0};
         pools[3] = Pool{d_out + r0 * w, (u32)w, 0};
-        int rc = run_level(ctx, d, key, d.gates, 1, pools, rows, nullptr, UINT32_MAX, shape); if (rc) return rc;
+        int rc = run_level(ctx, d, Exec{d.stream, d.slots, d.ext}, key, d.gates, 1, pools, rows, nullptr, UINT32_MAX, shape); if (rc) return rc;
     }
     return HERDB_OK;
 }
@@ -957,15 +956,15 @@ extern "C" int herdb_eval_circuit_rows_dev(herdb_ctx* ctx, const char* session, 
     if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
     const u32 w = key->n + 1;
     std::vector<size_t> goff, ooff;
-    rc = upload_tables(ctx, d, {&cc}, &d.gates, &d.gates_cap, &d.outs, &d.outs_cap, goff, ooff); if (rc) return rc;
+    rc = upload_tables(ctx, d.stream, {&cc}, &d.gates, &d.gates_cap, &d.outs, &d.outs_cap, goff, ooff); if (rc) return rc;
     // rows are processed in chunks sized so that the slot file + extraction buffer fit the budget
     size_t chunk = std::max<size_t>(1, ctx->mem_budget / std::max<size_t>(1, scratch_per_row(cc, key->n)));
     if (cc.max_level_width) chunk = std::min<size_t>(chunk, (size_t)0x7FFFFFFF / cc.max_level_width);
     chunk = std::min(chunk, n_rows);
-    rc = ensure_scratch(ctx, d, cc, key->n, chunk); if (rc) return rc;
+    rc = ensure_scratch(ctx, &d.slots, &d.slots_bytes, &d.ext, &d.ext_bytes, cc, key->n, chunk); if (rc) return rc;
     for (size_t r0 = 0; r0 < n_rows; r0 += chunk) {
         const u32 rows = (u32)std::min(chunk, n_rows - r0);
-        rc = issue_circuit(ctx, d, *key, cc, d.gates, d.outs, Pool{const_cast<u16*>(d_rows_in) + r0 * cc.in_bits * w, cc.in_bits * w, 0},
+        rc = issue_circuit(ctx, d, Exec{d.stream, d.slots, d.ext}, *key, cc, d.gates, d.outs, Pool{const_cast<u16*>(d_rows_in) + r0 * cc.in_bits * w, cc.in_bits * w, 0},
                            Pool{d_rows_out + r0 * cc.out_bits * w, cc.out_bits * w, 0}, false, rows);
         if (rc) return rc;
     }

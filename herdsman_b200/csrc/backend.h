@@ -29,18 +29,26 @@ struct DeviceKey {
     u32 ks_stride = 0;
 };
 
-// One pipelined evaluation's own buffers on one device (a task of either worker thread, or a caller of the
-// host-buffer entry points): double-buffered pinned host staging + device rows, the gate tables of its
-// circuit(s), and the events that order uploads, kernels and downloads of consecutive row chunks.
+// One pipelined evaluation's own resources on one device (a task of either task thread, or a caller of the
+// host-buffer entry points).  Row chunks alternate between two halves; each half has its own kernel stream, scratch
+// (slot file, extraction buffer), pinned host staging and device row buffers, so the levels of chunk c and of chunk
+// c+1 are in flight at the same time: when a level's last grid round leaves SMs empty, CTAs of the other chunk's
+// kernel take them (the blind-rotation kernel holds one CTA per SM, so two kernels share the GPU SM by SM).
+struct LaneHalf {
+    cudaStream_t stream = nullptr;                      // kernels of the chunks with this parity
+    u16* slots = nullptr; size_t slots_bytes = 0;
+    u16* ext = nullptr;   size_t ext_bytes = 0;
+    void* h_in = nullptr;  size_t h_in_cap = 0;         // pinned host: framed file bytes / staged caller rows
+    void* h_out = nullptr; size_t h_out_cap = 0;
+    u16* d_in = nullptr;   size_t d_in_cap = 0;
+    u16* d_out = nullptr;  size_t d_out_cap = 0;
+    u16* d_mid[2] = {};    size_t d_mid_cap[2] = {};    // rows between chained map stages (never leave HBM)
+    cudaEvent_t ev_in = nullptr, ev_done = nullptr, ev_out = nullptr;
+};
 struct Lane {
-    void* h_in[2] = {};   size_t h_in_cap[2] = {};      // pinned host: framed file bytes / staged caller rows
-    void* h_out[2] = {};  size_t h_out_cap[2] = {};
-    u16* d_in[2] = {};    size_t d_in_cap[2] = {};
-    u16* d_out[2] = {};   size_t d_out_cap[2] = {};
-    u16* d_mid[2] = {};   size_t d_mid_cap[2] = {};     // rows between chained map stages (never leave HBM)
+    LaneHalf half[2];
     GateDesc* gates = nullptr; size_t gates_cap = 0;
     OutDesc* outs = nullptr;   size_t outs_cap = 0;
-    cudaEvent_t ev_in[2] = {}, ev_done[2] = {}, ev_out[2] = {};
     bool busy = false;
 };
 
