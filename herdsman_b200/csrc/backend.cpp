@@ -428,17 +428,16 @@ int make_plan(herdb_ctx* ctx, const herdb_circuit* const* circuits, size_t n_sta
         io_row = std::max(io_row, (size_t)std::max(plan.stages[k].in_bits, plan.stages[k].out_bits) * w * 2 + 4);
         widest = std::max(widest, plan.stages[k].max_level_width);
     }
-    size_t chunk = std::max<size_t>(1, std::min(ctx->mem_budget / (2 * scratch), ctx->io_budget / io_row));   // two chunks in flight
+    size_t chunk = std::max<size_t>(1, std::min(ctx->mem_budget / scratch, ctx->io_budget / io_row));
     chunk = std::min<size_t>(chunk, (size_t)0x7FFFFFFF / widest);
     chunk = std::min(chunk, std::max<size_t>(1, rows_dev));
-    size_t nch = (std::max<size_t>(1, rows_dev) + chunk - 1) / chunk;
-    if (nch < 2 && rows_dev >= 2) nch = 2;                                                  // two chunks: both kernel streams of a lane have work
+    const size_t nch = (std::max<size_t>(1, rows_dev) + chunk - 1) / chunk;
     chunk = (std::max<size_t>(1, rows_dev) + nch - 1) / nch;                                // equal chunks: no short last one
     SchedHint hint; hint.rows = chunk; hint.wave = ctx->devs.empty() ? 0 : (u32)ctx->devs[0]->sm_count * kBrCtsPerCta;
     for (size_t k = 0; k < n_stages && n_rows; ++k) {
         std::string err;
         CompiledCircuit cc;
-        if (compile_circuit(circuits[k], cc, err, hint) == HERDB_OK && 2 * scratch_per_row(cc, n) * chunk <= std::max(ctx->mem_budget, 2 * scratch_per_row(cc, n)))
+        if (compile_circuit(circuits[k], cc, err, hint) == HERDB_OK && scratch_per_row(cc, n) * chunk <= std::max(ctx->mem_budget, scratch_per_row(cc, n)))
             plan.stages[k] = std::move(cc);
     }
     plan.chunk_rows = chunk;
@@ -448,22 +447,19 @@ int make_plan(herdb_ctx* ctx, const herdb_circuit* const* circuits, size_t n_sta
 Lane* acquire_lane(Device& d) {                      // d.mu held
     for (Lane* L : d.lanes) if (!L->busy) { L->busy = true; return L; }
     Lane* L = new Lane; L->busy = true;
-    for (LaneHalf& h : L->half) {
-        cudaStreamCreateWithFlags(&h.stream, cudaStreamNonBlocking);
+    for (LaneHalf& h : L->half)
         for (cudaEvent_t* e : {&h.ev_in, &h.ev_done, &h.ev_out}) cudaEventCreateWithFlags(e, cudaEventDisableTiming);
-    }
     d.lanes.push_back(L);
     return L;
 }
 void free_lane(Lane* L) {
     for (LaneHalf& h : L->half) {
-        if (h.stream) { cudaStreamSynchronize(h.stream); cudaStreamDestroy(h.stream); }
         if (h.h_in) cudaFreeHost(h.h_in);
         if (h.h_out) cudaFreeHost(h.h_out);
-        cudaFree(h.slots); cudaFree(h.ext); cudaFree(h.d_in); cudaFree(h.d_out); cudaFree(h.d_mid[0]); cudaFree(h.d_mid[1]);
+        cudaFree(h.d_in); cudaFree(h.d_out);
         for (cudaEvent_t e : {h.ev_in, h.ev_done, h.ev_out}) if (e) cudaEventDestroy(e);
     }
-    cudaFree(L->gates); cudaFree(L->outs);
+    cudaFree(L->d_mid[0]); cudaFree(L->d_mid[1]); cudaFree(L->gates); cudaFree(L->outs);
     delete L;
 }
 
@@ -497,7 +493,7 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
     const size_t in_stride = in_payload + (in_framed ? 4 : 0), out_stride = out_payload + (out_framed ? 4 : 0);
     size_t mid_row = 0;
     for (size_t k = 0; k + 1 < S; ++k) mid_row = std::max(mid_row, (size_t)plan.stages[k].out_bits * w * 2);
-    // equal chunks (make_plan), at least two when there are two rows: consecutive chunks run on the lane's two kernel streams
+    // equal chunks (make_plan)
     const size_t chunk = std::max<size_t>(1, std::min(plan.chunk_rows, rows));
     const size_t nch = (rows + chunk - 1) / chunk;
     const bool stage_in = !(io.src_mem && io.src_pinned), stage_out = !(io.dst_mem && io.dst_pinned);
@@ -519,17 +515,16 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
             if (!rc) rc = grow(ctx, (void**)&h.d_out, &h.d_out_cap, std::max<size_t>(16, chunk * out_stride));
             if (!rc && stage_in) rc = grow_pinned(ctx, &h.h_in, &h.h_in_cap, std::max<size_t>(16, chunk * in_stride));
             if (!rc && stage_out) rc = grow_pinned(ctx, &h.h_out, &h.h_out_cap, std::max<size_t>(16, chunk * out_stride));
-            for (int m = 0; m < 2 && !rc && S > 1; ++m) rc = grow(ctx, (void**)&h.d_mid[m], &h.d_mid_cap[m], std::max<size_t>(16, chunk * mid_row));
-            for (size_t k = 0; k < S && !rc; ++k) rc = ensure_scratch(ctx, &h.slots, &h.slots_bytes, &h.ext, &h.ext_bytes, plan.stages[k], plan.n, chunk);
         }
-        if (!rc) rc = upload_tables(ctx, L->half[0].stream, stage_ptrs, &L->gates, &L->gates_cap, &L->outs, &L->outs_cap, gate_off, out_off);
+        for (int m = 0; m < 2 && !rc && S > 1; ++m) rc = grow(ctx, (void**)&L->d_mid[m], &L->d_mid_cap[m], std::max<size_t>(16, chunk * mid_row));
+        for (size_t k = 0; k < S && !rc; ++k) rc = ensure_scratch(ctx, &d.slots, &d.slots_bytes, &d.ext, &d.ext_bytes, plan.stages[k], plan.n, chunk);
+        if (!rc) rc = upload_tables(ctx, d.stream, stage_ptrs, &L->gates, &L->gates_cap, &L->outs, &L->outs_cap, gate_off, out_off);
         if (rc) { L->busy = false; return rc; }
     }
     auto release = [&](int rc) {
         std::lock_guard<std::mutex> l(d.mu);
         cudaSetDevice(d.id);
-        for (LaneHalf& h : L->half) cudaStreamSynchronize(h.stream);             // nothing of this evaluation is in flight any more
-        cudaStreamSynchronize(d.copy); cudaStreamSynchronize(d.copy_out);
+        if (rc) { cudaStreamSynchronize(d.stream); cudaStreamSynchronize(d.copy); cudaStreamSynchronize(d.copy_out); }   // else: every chunk's download has been awaited
         drain_ready(d);
         L->busy = false;
         return rc;
@@ -562,17 +557,17 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
                 if (c >= 2) CU(cudaStreamWaitEvent(d.copy, h.ev_done, 0));               // kernels of chunk c-2 have read d_in
                 if (in_stride) CU(cudaMemcpyAsync(h.d_in, h_src, cnt * in_stride, cudaMemcpyHostToDevice, d.copy));
                 CU(cudaEventRecord(h.ev_in, d.copy));
-                CU(cudaStreamWaitEvent(h.stream, h.ev_in, 0));
-                if (c >= 2) CU(cudaStreamWaitEvent(h.stream, h.ev_out, 0));               // download of chunk c-2 has read d_out
-                const Exec ex{h.stream, h.slots, h.ext};
+                CU(cudaStreamWaitEvent(d.stream, h.ev_in, 0));
+                if (c >= 2) CU(cudaStreamWaitEvent(d.stream, h.ev_out, 0));               // download of chunk c-2 has read d_out
+                const Exec ex{d.stream, d.slots, d.ext};
                 for (size_t k = 0; k < S; ++k) {
                     const CompiledCircuit& cc = plan.stages[k];
-                    Pool in = k == 0 ? Pool{h.d_in + (in_framed ? 2 : 0), (u32)(in_stride / 2), 0} : Pool{h.d_mid[(k - 1) & 1], cc.in_bits * (u32)w, 0};
-                    Pool out = k + 1 == S ? Pool{h.d_out + (out_framed ? 2 : 0), (u32)(out_stride / 2), 0} : Pool{h.d_mid[k & 1], cc.out_bits * (u32)w, 0};
+                    Pool in = k == 0 ? Pool{h.d_in + (in_framed ? 2 : 0), (u32)(in_stride / 2), 0} : Pool{L->d_mid[(k - 1) & 1], cc.in_bits * (u32)w, 0};
+                    Pool out = k + 1 == S ? Pool{h.d_out + (out_framed ? 2 : 0), (u32)(out_stride / 2), 0} : Pool{L->d_mid[k & 1], cc.out_bits * (u32)w, 0};
                     int r2 = issue_circuit(ctx, d, ex, *key, cc, L->gates + gate_off[k], L->outs + out_off[k], in, out, k + 1 == S && out_framed, (u32)cnt);
                     if (r2) return r2;
                 }
-                CU(cudaEventRecord(h.ev_done, h.stream));
+                CU(cudaEventRecord(h.ev_done, d.stream));
                 CU(cudaStreamWaitEvent(d.copy_out, h.ev_done, 0));
                 void* h_dst = stage_out ? h.h_out : (void*)(io.dst_mem + row * out_stride);
                 if (out_stride) CU(cudaMemcpyAsync(h_dst, h.d_out, cnt * out_stride, cudaMemcpyDeviceToHost, d.copy_out));
@@ -616,7 +611,13 @@ int eval_rows_pipelined(herdb_ctx* ctx, const char* session, const EvalPlan& pla
         for (size_t di = 0; di < G; ++di) th.emplace_back(run_slice, di);
         for (auto& t : th) t.join();
     }
-    for (int rc : rcs) if (rc) return rc;                // (the timing intervals of this evaluation are in the stats: release())
+    for (size_t di = 0; di < G; ++di) {                  // timing intervals of this evaluation are in the stats when the call returns
+        Device& d = *ctx->devs[di];
+        std::lock_guard<std::mutex> l(d.mu);
+        cudaSetDevice(d.id);
+        drain_ready(d);
+    }
+    for (int rc : rcs) if (rc) return rc;
     return HERDB_OK;
 }
 

@@ -29,24 +29,23 @@ struct DeviceKey {
     u32 ks_stride = 0;
 };
 
-// One pipelined evaluation's own resources on one device (a task of either task thread, or a caller of the
-// host-buffer entry points).  Row chunks alternate between two halves; each half has its own kernel stream, scratch
-// (slot file, extraction buffer), pinned host staging and device row buffers, so the levels of chunk c and of chunk
-// c+1 are in flight at the same time: when a level's last grid round leaves SMs empty, CTAs of the other chunk's
-// kernel take them (the blind-rotation kernel holds one CTA per SM, so two kernels share the GPU SM by SM).
+// One pipelined evaluation's own buffers on one device (a task of either task thread, or a caller of the host-buffer
+// entry points): pinned host staging and device row buffers for two row chunks (double buffering), the gate tables of
+// its circuit(s), and the events that order uploads, kernels and downloads of consecutive chunks.  Kernels of every
+// lane go to the device's one kernel stream: a second kernel stream per lane (consecutive chunks in flight together,
+// to fill part-empty grid rounds) was measured and is slower -- the persistent blind-rotation kernel holds every SM, so
+// the other stream's key switch cannot start before it ends and the streams serialise, at half the jobs per launch
+// (profiles/r02d_two_streams_*.json*).
 struct LaneHalf {
-    cudaStream_t stream = nullptr;                      // kernels of the chunks with this parity
-    u16* slots = nullptr; size_t slots_bytes = 0;
-    u16* ext = nullptr;   size_t ext_bytes = 0;
     void* h_in = nullptr;  size_t h_in_cap = 0;         // pinned host: framed file bytes / staged caller rows
     void* h_out = nullptr; size_t h_out_cap = 0;
     u16* d_in = nullptr;   size_t d_in_cap = 0;
     u16* d_out = nullptr;  size_t d_out_cap = 0;
-    u16* d_mid[2] = {};    size_t d_mid_cap[2] = {};    // rows between chained map stages (never leave HBM)
     cudaEvent_t ev_in = nullptr, ev_done = nullptr, ev_out = nullptr;
 };
 struct Lane {
     LaneHalf half[2];
+    u16* d_mid[2] = {};    size_t d_mid_cap[2] = {};    // rows between chained map stages (never leave HBM)
     GateDesc* gates = nullptr; size_t gates_cap = 0;
     OutDesc* outs = nullptr;   size_t outs_cap = 0;
     bool busy = false;
