@@ -171,7 +171,12 @@ def circuits_block(be, sk, args):
     out = {}
 
     def run(name, cfg, stages, cols, bits, plain, seed, rows, cmp_rows, cpu_1t_rows):
-        rows_in = _enc_cols(cs, cm, sk, cols, bits, seed)
+        import torch
+        rows_np = _enc_cols(cs, cm, sk, cols, bits, seed)
+        pin = torch.empty(rows_np.shape, dtype=torch.uint16, pin_memory=True)       # page-locked host rows, as the e2e headline uses
+        pin.numpy()[:] = rows_np
+        rows_in = pin.numpy()
+        del rows_np
         gates_per_row = sum(api.analyze(c)["boot_gates"] for c in stages)
         ev = (lambda r=rows_in: be.eval_circuit_rows("bench", stages[0], r)) if len(stages) == 1 else (lambda r=rows_in: be.eval_pipeline_rows("bench", stages, r))
         ev(rows_in[:64])                                           # allocations
@@ -249,7 +254,7 @@ def strong_block(be, sk, args, rank, world, dist, dev, barrier):
         if total % world == 0:
             mine = h_out.to(dev)
             gathered = torch.empty((total, 1, w), dtype=torch.uint16, device=dev)
-            dist.all_gather_into_tensor(gathered.view(torch.int16), mine.view(torch.int16))
+            dist.all_gather_into_tensor(gathered.view(torch.uint8), mine.view(torch.uint8))     # NCCL has no 16-bit integer type
             all_rows = gathered.cpu().numpy()
         else:
             parts = [None] * world
@@ -357,7 +362,12 @@ def run_ours(args, rank, world, local_rank):
 
     strong = None
     if args.strong_rows and not (world == 1 and args.circuits == "off"):
-        strong = strong_block(be, sk, args, rank, world, dist, dev, barrier)
+        try:                                            # never lose the headline line to a side block
+            strong = strong_block(be, sk, args, rank, world, dist, dev, barrier)
+        except Exception as e:                          # noqa: BLE001
+            strong = {"error": "%s: %s" % (type(e).__name__, e)}
+            if dist is not None:                        # the ranks may no longer be in step: skip the final barrier
+                dist = None
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -421,7 +431,10 @@ def run_ours(args, rank, world, local_rank):
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(be, sk, args)
     if world == 1 and args.circuits != "off":
-        line["circuits"] = circuits_block(be, sk, args)
+        try:
+            line["circuits"] = circuits_block(be, sk, args)
+        except Exception as e:                          # noqa: BLE001
+            line["circuits"] = {"error": "%s: %s" % (type(e).__name__, e)}
     emit(line)
 
 
