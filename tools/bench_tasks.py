@@ -32,7 +32,17 @@ import clientsim as cs  # noqa: E402
 N = 512
 
 
+_OUT = None
+
+
+def emit(line):
+    os.write(_OUT, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.dup(1); os.dup2(2, 1)                     # NCCL prints its version banner on fd 1: keep stdout for the JSON lines
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", default="pipeline", choices=["lt32", "pipeline", "add8"])
     ap.add_argument("--rows", type=int, default=16384)
@@ -120,7 +130,7 @@ def run_big(args, root):
                      "file_bytes_read": in_bytes, "file_bytes_written": R * (4 + (N + 1) * 2),
                      "gates_per_device": [s["gates_bootstrapped"] for s in st]},
             "all_rows_decrypt_to_plaintext": ok, "output_sha256": h.hexdigest()}
-    print(json.dumps(line), flush=True)
+    emit(line)
     wg.close()
     if not ok:
         raise SystemExit("bench_tasks: wrong rows")
@@ -205,7 +215,7 @@ def run(args, root):
             "seam_over_host": t_host / t_seam,
             "decrypt_matches_plaintext": ok, "seam_rows_equal_host_rows": same,
             "output_sha256": hashlib.sha256(got.tobytes()).hexdigest()}
-    print(json.dumps(line), flush=True)
+    emit(line)
     wg.close()
     if not (ok and same):
         raise SystemExit("bench_tasks: wrong rows")
