@@ -25,6 +25,7 @@ _lib = None
 N_STD128 = 512
 N_TEST = 32
 RING_N = 1024
+NOALLOC_MAX_BATCH = 2368        # HERDB_NOALLOC_MAX_BATCH (include/herdb_params.h)
 GATE = {"OR": 0, "AND": 1, "NOR": 2, "NAND": 3, "XOR_FAST": 4, "XNOR_FAST": 5}
 EXPORTS = [
     "herdb_create", "herdb_destroy", "herdb_strerror", "herdb_last_error", "herdb_device_count",
@@ -33,7 +34,7 @@ EXPORTS = [
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_pipeline_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_circuit_schedule", "herdb_circuit_eval_plain", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_task_threads", "herdb_key_blob_size", "herdb_loaded_keys", "herdb_partition_count", "herdb_eval_gate_batch_dev_shape",
-    "herdb_measure_l2_bandwidth",
+    "herdb_measure_l2_bandwidth", "herdb_eval_gate_batch_dev_noalloc",
 ]
 
 
@@ -98,6 +99,7 @@ def lib():
         L.herdb_reset_stats.argtypes = [vp]
         L.herdb_measure_int_peak.argtypes = [vp, ci] + [C.POINTER(C.c_double)] * 5
         L.herdb_measure_l2_bandwidth.argtypes = [vp, ci, C.POINTER(C.c_double)]
+        L.herdb_eval_gate_batch_dev_noalloc.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz]
         L.herdb_task_threads.argtypes = [vp]
         L.herdb_key_blob_size.argtypes = [u32]; L.herdb_key_blob_size.restype = sz
         L.herdb_loaded_keys.argtypes = [vp]
@@ -256,6 +258,11 @@ class Backend:
             self._check(self.L.herdb_eval_gate_batch_dev_shape(self.h, session.encode(), device, g, _ptr(d_a), _ptr(d_b), _ptr(d_out), batch, shape))
         else:
             self._check(self.L.herdb_eval_gate_batch_dev(self.h, session.encode(), device, g, _ptr(d_a), _ptr(d_b), _ptr(d_out), batch))
+
+    def eval_gate_batch_dev_noalloc(self, session, gate, d_a, d_b, d_out, batch, device=0):
+        """herdb_eval_gate_batch_dev_noalloc: no allocation on the call path, batch <= NOALLOC_MAX_BATCH"""
+        g = GATE[gate] if isinstance(gate, str) else int(gate)
+        self._check(self.L.herdb_eval_gate_batch_dev_noalloc(self.h, session.encode(), device, g, _ptr(d_a), _ptr(d_b), _ptr(d_out), batch))
 
     def eval_circuit_rows(self, session, circuit: Circuit, rows_in, out=None):
         n = self.key_lwe_n(session)

@@ -885,6 +885,54 @@ extern "C" int herdb_eval_gate_batch_dev_shape(herdb_ctx* ctx, const char* sessi
     return gate_batch_dev(ctx, session, device, gate, d_a, d_b, d_out, batch, cts_per_cta);
 }
 
+// The same single-gate batch with NO allocation anywhere on the call path (no cudaMalloc / cudaFree / event creation):
+// the extraction buffer and the gate descriptor are the library's static device arrays (kernels.cu), whose device
+// addresses are looked up once per device.  No counterpart in the reference; added
+// for callers that cannot allocate (CUDA graph capture, tight serving loops).  Kernel timing events are not recorded on
+// this path (creating them allocates); launches and gates are still counted.
+extern "C" int herdb_eval_gate_batch_dev_noalloc(herdb_ctx* ctx, const char* session, int device, int gate,
+                                                 const uint16_t* d_a, const uint16_t* d_b, uint16_t* d_out, size_t batch) {
+    if (!ctx || !session || device < 0 || device >= (int)ctx->devs.size() || gate < 0 || gate > HERDB_GATE_XNOR_FAST) return HERDB_ERR_ARG;
+    if (batch > HERDB_NOALLOC_MAX_BATCH) {
+        ctx->set_error("herdb_eval_gate_batch_dev_noalloc: batch of " + std::to_string(batch) + " gates exceeds HERDB_NOALLOC_MAX_BATCH = " +
+                       std::to_string(HERDB_NOALLOC_MAX_BATCH) + " (the scratch is a fixed array; use herdb_eval_gate_batch_dev, or split the batch)");
+        return HERDB_ERR_ARG;
+    }
+    if (!batch) return HERDB_OK;
+    if (!d_a || !d_b || !d_out) return HERDB_ERR_ARG;
+    Device& d = *ctx->devs[device];
+    std::lock_guard<std::mutex> l(d.mu);
+    CU(cudaSetDevice(d.id));
+    if (!d.noalloc_ready) {                          // set-up, once per device, with that device current
+        CU(noalloc_setup(&d.noalloc_ext, &d.noalloc_gate));
+        d.noalloc_ready = true;
+    }
+    const DeviceKey* key = find_key(d, session);
+    if (!key) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
+    const u32 w = key->n + 1, jobs = (u32)batch;
+    GateDesc g{}; g.gate = (uint8_t)gate; g.pool_a = 0; g.pool_b = 2; g.pool_out = 3;
+    CU(launch_noalloc_set_gate(g, d.stream));        // by value through the kernel parameters: no staging copy
+    Pool pools[4] = {};
+    pools[0] = Pool{const_cast<u16*>(d_a), w, 0};
+    pools[2] = Pool{const_cast<u16*>(d_b), w, 0};
+    pools[3] = Pool{d_out, w, 0};
+    BrParams bp{};
+    bp.bsk = key->bsk; bp.mono = d.mono; bp.ftw2 = d.ftw2; bp.itw1 = d.itw1; bp.gates = d.noalloc_gate;
+    for (int i = 0; i < 4; ++i) bp.pools[i] = pools[i];
+    bp.ext = d.noalloc_ext; bp.trace = nullptr; bp.n = key->n; bp.steps = key->n; bp.rows = jobs; bp.jobs = jobs; bp.job0 = 0; bp.job1 = jobs;
+    int launches = 0;
+    CU(launch_blind_rotate(bp, d.sm_count, d.stream, 0, &launches));
+    KsParams kp{};
+    kp.ksk = key->ksk; kp.ext = d.noalloc_ext; kp.gates = d.noalloc_gate;
+    for (int i = 0; i < 4; ++i) kp.pools[i] = pools[i];
+    kp.ks_stride = key->ks_stride; kp.n = key->n; kp.rows = jobs; kp.jobs = jobs;
+    CU(launch_keyswitch(kp, d.sm_count, d.stream));
+    d.stats.kernel_launches += (uint64_t)launches + 2;
+    d.stats.gates_bootstrapped += jobs;
+    CU(cudaStreamSynchronize(d.stream));
+    return HERDB_OK;
+}
+
 // Host buffers.  A large batch is cut into a head of one grid round, a middle and a tail of one round (+ the
 // remainder): the middle's upload rides the copy stream under the head's kernels and the middle's download
 // under the tail's, so only one round's worth of PCIe traffic is exposed.  Pieces are multiples of the round

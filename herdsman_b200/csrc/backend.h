@@ -67,6 +67,8 @@ struct Device {
     OutDesc* outs = nullptr;   size_t outs_cap = 0;
     u16* io_in = nullptr;  size_t io_in_bytes = 0;     // staging of herdb_eval_gate_batch
     u16* io_out = nullptr; size_t io_out_bytes = 0;
+    // herdb_eval_gate_batch_dev_noalloc: device addresses of the library's static scratch (looked up once per device)
+    u16* noalloc_ext = nullptr; GateDesc* noalloc_gate = nullptr; bool noalloc_ready = false;
     std::vector<Lane*> lanes;
     // timing: CUDA events around the two hot kernels, summed into `stats` once they have completed
     struct Timed { cudaEvent_t a, b; int kind; };

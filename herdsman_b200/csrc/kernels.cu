@@ -242,6 +242,21 @@ __global__ void __launch_bounds__(256) l2_read_kernel(const uint4* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Scratch for the entry point that allocates nothing (herdb_eval_gate_batch_dev_noalloc, include/herdb.h): the
+// extraction buffer between blind rotation and key switch -- [jobs][kExtStride] u16, cudaMalloc'ed and grown on demand
+// on every other path -- lives here in a file-scope array of fixed size, HERDB_NOALLOC_MAX_BATCH jobs (4.66 MiB; every
+// GPU that loads the library holds it until exit), next to the one gate descriptor such a launch needs.
+// In HOST code these names are host-side stand-ins, not device addresses: noalloc_setup() asks the runtime for the
+// device addresses (cudaGetSymbolAddress, once per device, with that device current) and the kernels are given those.
+// Nothing in the buffer has to start at zero: blind rotation writes words 0..N of every job before the key switch
+// reads them and the padding words are never read, so the previous call's contents are harmless.  All calls on a
+// device share the array: calls that overlap on the GPU (other streams, other contexts) race.
+static __device__ __align__(256) u16 g_noalloc_ext[(size_t)HERDB_NOALLOC_MAX_BATCH * kExtStride];
+static __device__ __align__(16) GateDesc g_noalloc_gate;
+
+__global__ void noalloc_set_gate_kernel(GateDesc g) { g_noalloc_gate = g; }      // device code names the array directly
+
+// ------------------------------------------------------------------------------------------------
 // launchers (plain C++ signatures so backend.cpp does not need nvcc)
 template <int C>
 static cudaError_t launch_br(BrParams P, u32 job0, u32 job1, int sm_count, cudaStream_t stream) {
@@ -303,6 +318,15 @@ cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 pol
 }
 cudaError_t launch_ksk_relayout(const u16* in, u16* out, u32 n, u32 stride, size_t rows, int sm_count, cudaStream_t stream) {
     ksk_relayout_kernel<<<sm_count * 8, 256, 0, stream>>>(in, out, n, stride, rows);
+    return cudaGetLastError();
+}
+cudaError_t noalloc_setup(u16** ext_out, GateDesc** gate_out) {               // the device in question is current
+    cudaError_t e = cudaGetSymbolAddress((void**)ext_out, g_noalloc_ext);
+    if (e != cudaSuccess) return e;
+    return cudaGetSymbolAddress((void**)gate_out, g_noalloc_gate);
+}
+cudaError_t launch_noalloc_set_gate(const GateDesc& g, cudaStream_t stream) {
+    noalloc_set_gate_kernel<<<1, 1, 0, stream>>>(g);
     return cudaGetLastError();
 }
 cudaError_t launch_l2_read(const void* buf, size_t bytes, int reps, u32* out, int sm_count, cudaStream_t stream) {

@@ -28,6 +28,9 @@ cudaError_t launch_keyswitch(const KsParams& P, int sm_count, cudaStream_t strea
 cudaError_t launch_gather_outputs(const GatherParams& P, int sm_count, cudaStream_t stream);
 cudaError_t launch_bsk_convert(const u32* in, u32* out, const u32* ftw2, u32 polys, int sm_count, cudaStream_t stream);
 cudaError_t launch_ksk_relayout(const u16* in, u16* out, u32 n, u32 stride, size_t rows, int sm_count, cudaStream_t stream);
+// the no-allocation entry point (kernels.cu, "Scratch for the entry point that allocates nothing")
+cudaError_t noalloc_setup(u16** ext_out, GateDesc** gate_out);
+cudaError_t launch_noalloc_set_gate(const GateDesc& g, cudaStream_t stream);
 cudaError_t launch_l2_read(const void* buf, size_t bytes, int reps, u32* out, int sm_count, cudaStream_t stream);
 cudaError_t launch_int_peak(int mode, u32* out, int blocks, int iters, cudaStream_t stream);
 

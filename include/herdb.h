@@ -221,6 +221,20 @@ int herdb_eval_gate_batch_dev_shape(herdb_ctx* ctx, const char* session_uuid, in
                                     const uint16_t* d_ct_a, const uint16_t* d_ct_b, uint16_t* d_ct_out,
                                     size_t batch, int cts_per_cta);
 
+/* herdb_eval_gate_batch_dev for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and ciphertexts as herdb_eval_gate_batch_dev; the call path contains no cudaMalloc, cudaFree,
+ * event creation or other allocating routine.  The scratch the two kernels share (the extraction buffer between blind
+ * rotation and key switch) is a fixed array in the library's device image: 4.66 MiB that every GPU which loads the
+ * library holds until exit, enough for batch <= HERDB_NOALLOC_MAX_BATCH (2,368 gates, herdb_params.h).  A larger batch is
+ * refused with HERDB_ERR_ARG and a message in herdb_last_error.  All calls on a device share that array (it keeps the
+ * last call's contents, which is harmless: every word read is written first): calls of one context are serialised by
+ * the library, but calls that overlap on the GPU -- two contexts on one device -- race.  Kernel times of this path are
+ * not added to herdb_stats (timing events would have to be created); launches and gates are counted. */
+int herdb_eval_gate_batch_dev_noalloc(herdb_ctx* ctx, const char* session_uuid, int device, int gate,
+                                      const uint16_t* d_ct_a, const uint16_t* d_ct_b, uint16_t* d_ct_out,
+                                      size_t batch);
+
 /* circuit facts (host-only, no device needed): bootstrapped gates per row, levels, slots */
 typedef struct herdb_circuit_info {
     uint32_t in_bits, out_bits;     /* ciphertexts per input / output row                      */
