@@ -34,7 +34,7 @@ EXPORTS = [
     "herdb_eval_gate_batch", "herdb_eval_circuit_rows", "herdb_eval_pipeline_rows", "herdb_eval_gate_batch_dev", "herdb_eval_circuit_rows_dev",
     "herdb_circuit_analyze", "herdb_circuit_schedule", "herdb_circuit_eval_plain", "herdb_get_stats", "herdb_get_stream", "herdb_reset_stats", "herdb_measure_int_peak",
     "herdb_task_threads", "herdb_key_blob_size", "herdb_loaded_keys", "herdb_partition_count", "herdb_eval_gate_batch_dev_shape",
-    "herdb_measure_l2_bandwidth", "herdb_eval_gate_batch_dev_noalloc",
+    "herdb_measure_l2_bandwidth", "herdb_eval_gate_batch_dev_noalloc", "herdb_task_window",
 ]
 
 
@@ -101,6 +101,7 @@ def lib():
         L.herdb_measure_l2_bandwidth.argtypes = [vp, ci, C.POINTER(C.c_double)]
         L.herdb_eval_gate_batch_dev_noalloc.argtypes = [vp, cp, ci, ci, vp, vp, vp, sz]
         L.herdb_task_threads.argtypes = [vp]
+        L.herdb_task_window.argtypes = [vp]
         L.herdb_key_blob_size.argtypes = [u32]; L.herdb_key_blob_size.restype = sz
         L.herdb_loaded_keys.argtypes = [vp]
         L.herdb_partition_count.argtypes = [cp, sz, C.POINTER(u64)]
@@ -235,6 +236,9 @@ class Backend:
 
     def task_threads(self):
         return self.L.herdb_task_threads(self.h)
+
+    def task_window(self):
+        return self.L.herdb_task_window(self.h)
 
     def key_lwe_n(self, session):
         n = C.c_uint32()
@@ -411,7 +415,7 @@ class CudaWorkerGroup:
 
     def __init__(self, storage_dir, key_dir, devices=(0,)):
         self.backend = Backend(devices, storage_dir, key_dir)
-        self._concurrent = self.backend.task_threads()      # tasks the backend really runs at once
+        self._concurrent = self.backend.task_window()       # tasks to keep outstanding: task threads + a queue to coalesce from
         self._handles = {}
         self._next = 1
         self._lock = threading.Lock()

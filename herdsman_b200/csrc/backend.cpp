@@ -390,9 +390,11 @@ void unpin_session_key(herdb_ctx* ctx, const std::string& session) {
 //     byte image ([u32 length][payload] per row, storage_service.cpp:19-28) and the output kernel writes the
 //     framed image of the output partition, so the host touches no row: pread -> cudaMemcpyAsync, and
 //     cudaMemcpyAsync -> pwrite.
+struct FileSeg { int src_fd; int dst_fd; size_t rows; };    // one task's input partition file, its output file, its rows
 struct RowIo {
-    const uint8_t* src_mem = nullptr; int src_fd = -1;      // dense rows in host memory, or a partition file
-    uint8_t* dst_mem = nullptr;       int dst_fd = -1;
+    const uint8_t* src_mem = nullptr;                        // dense rows in host memory ...
+    uint8_t* dst_mem = nullptr;
+    std::vector<FileSeg> files;                              // ... or partition files: the rows of several coalesced tasks, concatenated
     bool src_pinned = false, dst_pinned = false;             // caller memory is page-locked: DMA straight from / to it
 };
 struct EvalPlan {
@@ -482,13 +484,29 @@ int full_pwrite(int fd, const void* buf, size_t len, off_t off) {
     return 0;
 }
 
+// rows [row, row + cnt) of the concatenated file segments <-> buf (`stride` bytes per framed row)
+int files_rw(const RowIo& io, size_t row, size_t cnt, size_t stride, void* buf, bool write) {
+    size_t seg0 = 0;
+    for (const FileSeg& sg : io.files) {
+        const size_t lo = std::max(row, seg0), hi = std::min(row + cnt, seg0 + sg.rows);
+        if (lo < hi) {
+            char* p = (char*)buf + (lo - row) * stride;
+            const off_t off = (off_t)((lo - seg0) * stride);
+            const int rc = write ? full_pwrite(sg.dst_fd, p, (hi - lo) * stride, off) : full_pread(sg.src_fd, p, (hi - lo) * stride, off);
+            if (rc) return rc;
+        }
+        seg0 += sg.rows;
+    }
+    return 0;
+}
+
 // rows [r0, r0 + rows) of the task on one device
 int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPlan& plan, const RowIo& io, size_t r0, size_t rows) {
     if (!rows) return HERDB_OK;
     NvtxRange range("herdb:device_slice");
     const size_t S = plan.stages.size(), w = plan.n + 1;
     const CompiledCircuit& first = plan.stages.front(); const CompiledCircuit& last = plan.stages.back();
-    const bool in_framed = io.src_fd >= 0, out_framed = io.dst_fd >= 0;
+    const bool in_framed = !io.files.empty(), out_framed = !io.files.empty();
     const size_t in_payload = (size_t)first.in_bits * w * 2, out_payload = (size_t)last.out_bits * w * 2;
     const size_t in_stride = in_payload + (in_framed ? 4 : 0), out_stride = out_payload + (out_framed ? 4 : 0);
     size_t mid_row = 0;
@@ -540,7 +558,7 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
                 if (stage_in) {
                     if (c >= 2 && cudaEventSynchronize(h.ev_in) != cudaSuccess) { ctx->set_error("upload failed"); rc = HERDB_ERR_CUDA; break; }
                     if (in_framed) {
-                        if (full_pread(io.src_fd, h.h_in, cnt * in_stride, (off_t)(row * in_stride)) != 0) { ctx->set_error("short read of the input partition"); rc = HERDB_ERR_IO; break; }
+                        if (files_rw(io, row, cnt, in_stride, h.h_in, false) != 0) { ctx->set_error("short read of the input partition"); rc = HERDB_ERR_IO; break; }
                         for (size_t r = 0; r < cnt; ++r) {                                 // every row announces exactly the circuit's input row
                             uint32_t len; memcpy(&len, (const uint8_t*)h.h_in + r * in_stride, 4);
                             if (len != in_payload) { rc = HERDB_ERR_FORMAT; break; }
@@ -584,7 +602,7 @@ int device_pipeline(herdb_ctx* ctx, Device& d, const char* session, const EvalPl
             if (cudaEventSynchronize(h.ev_out) != cudaSuccess) { ctx->set_error(std::string("evaluation failed: ") + cudaGetErrorString(cudaGetLastError())); rc = HERDB_ERR_CUDA; break; }
             if (out_stride && stage_out) {
                 if (out_framed) {
-                    if (full_pwrite(io.dst_fd, h.h_out, cnt * out_stride, (off_t)(row * out_stride)) != 0) { ctx->set_error("cannot write the output partition"); rc = HERDB_ERR_IO; break; }
+                    if (files_rw(io, row, cnt, out_stride, h.h_out, true) != 0) { ctx->set_error("cannot write the output partition"); rc = HERDB_ERR_IO; break; }
                 } else memcpy(io.dst_mem + row * out_stride, h.h_out, cnt * out_stride);
             }
             std::lock_guard<std::mutex> l(d.mu);
@@ -704,6 +722,12 @@ extern "C" int herdb_create(herdb_ctx** out, const int* device_ids, int n_device
     ctx->mem_budget = env_mb("HERDB_MEM_BUDGET_MB", 16384);
     ctx->io_budget = env_mb("HERDB_IO_CHUNK_MB", 1024);
     ctx->key_budget = env_mb("HERDB_KEY_BUDGET_MB", 32768);
+    {
+        const char* cr = getenv("HERDB_COALESCE_ROWS");          // 0 switches task coalescing off
+        ctx->coalesce_rows = cr ? (uint64_t)std::max<long long>(0, atoll(cr)) : 4096;
+        const char* tw = getenv("HERDB_TASK_WINDOW");
+        ctx->task_window = std::max(1, std::min(64, tw ? atoi(tw) : 8));
+    }
     std::vector<int> ids;
     if (device_ids && n_devices > 0) ids.assign(device_ids, device_ids + n_devices); else ids.push_back(0);
     std::vector<u32> mono, ftw2(kLaneTwWords), itw1(kLaneTwWords);
@@ -737,6 +761,7 @@ extern "C" int herdb_create(herdb_ctx** out, const int* device_ids, int n_device
 }
 
 extern "C" int herdb_task_threads(const herdb_ctx* ctx) { return ctx ? (int)ctx->workers.size() : 0; }
+extern "C" int herdb_task_window(const herdb_ctx* ctx) { return ctx ? std::max(ctx->task_window, (int)ctx->workers.size()) : 0; }
 
 extern "C" void herdb_destroy(herdb_ctx* ctx) {
     if (!ctx) return;
@@ -1173,30 +1198,42 @@ struct OutFile {                                     // "<path>.tmp" until commi
     ~OutFile() { if (fd >= 0) { close(fd); remove(tmp.c_str()); } }
 };
 
-// MapTask: the input partition is streamed through the chunk pipeline, never held in memory as a whole
-int run_map_task(herdb_ctx* ctx, const TaskReq& t, u32 n) {
+// MapTask(s): the input partition is streamed through the chunk pipeline, never held in memory as a whole.  `ts` is one
+// task, or several queued tasks of one session with the same circuit that the worker coalesced (worker_loop): their
+// rows go through the levels as ONE batch -- a 128-row partition alone fills a fraction of a grid round per level --
+// while every task still reads its own partition file and writes (and commits) its own.
+int run_map_tasks(herdb_ctx* ctx, const std::vector<const TaskReq*>& ts, u32 n) {
     NvtxRange range("herdb:map_task");
-    const herdb_circuit view = t.circuit.view();
+    const TaskReq& t0 = *ts[0];
+    const herdb_circuit view = t0.circuit.view();
     const herdb_circuit* cp = &view;
+    uint64_t total = 0;
+    for (const TaskReq* t : ts) total += t->row_count;
     EvalPlan plan;
-    int rc = make_plan(ctx, &cp, 1, t.row_count, n, plan); if (rc) return rc;
+    int rc = make_plan(ctx, &cp, 1, total, n, plan); if (rc) return rc;
     const size_t w = n + 1, in_stride = (size_t)plan.stages[0].in_bits * w * 2 + 4;
-    const std::string in_path = partition_path(ctx, t.session, t.in_df, t.in_part);
-    const int fd = open(in_path.c_str(), O_RDONLY);
-    if (fd < 0) { ctx->set_error("cannot open partition " + in_path); return HERDB_ERR_IO; }
-    struct stat st{};
-    if (fstat(fd, &st) != 0 || (uint64_t)st.st_size != t.row_count * in_stride) {            // row_count rows of the circuit's input row, exactly
-        close(fd);
-        ctx->set_error("partition " + in_path + ": row count / row length does not match the task (row_count, circuit inputs)");
-        return HERDB_ERR_FORMAT;
+    RowIo io;
+    std::deque<OutFile> outs;
+    auto close_inputs = [&] { for (const FileSeg& sg : io.files) close(sg.src_fd); };
+    for (const TaskReq* t : ts) {
+        const std::string in_path = partition_path(ctx, t->session, t->in_df, t->in_part);
+        const int fd = open(in_path.c_str(), O_RDONLY);
+        if (fd < 0) { close_inputs(); ctx->set_error("cannot open partition " + in_path); return HERDB_ERR_IO; }
+        struct stat st{};
+        if (fstat(fd, &st) != 0 || (uint64_t)st.st_size != t->row_count * in_stride) {       // row_count rows of the circuit's input row, exactly
+            close(fd); close_inputs();
+            ctx->set_error("partition " + in_path + ": row count / row length does not match the task (row_count, circuit inputs)");
+            return HERDB_ERR_FORMAT;
+        }
+        outs.emplace_back();
+        rc = outs.back().open_tmp(ctx, partition_path(ctx, t->session, t->out_df, t->out_part));
+        if (rc) { close(fd); close_inputs(); return rc; }
+        io.files.push_back(FileSeg{fd, outs.back().fd, (size_t)t->row_count});
     }
-    OutFile out;
-    rc = out.open_tmp(ctx, partition_path(ctx, t.session, t.out_df, t.out_part));
-    if (rc) { close(fd); return rc; }
-    RowIo io; io.src_fd = fd; io.dst_fd = out.fd;
-    rc = eval_rows_pipelined(ctx, t.session.c_str(), plan, io, t.row_count);
-    close(fd);
-    return rc ? rc : out.commit(ctx);
+    rc = eval_rows_pipelined(ctx, t0.session.c_str(), plan, io, total);
+    close_inputs();
+    for (OutFile& o : outs) { if (rc) break; rc = o.commit(ctx); }
+    return rc;
 }
 
 // a reduce circuit takes two rows of the output layout: inputs[0] == inputs[1] == output column types
@@ -1263,13 +1300,20 @@ int run_reduce_task(herdb_ctx* ctx, const TaskReq& t, u32 n) {
     return rc;
 }
 
-int run_task(herdb_ctx* ctx, const TaskReq& t) {
+int run_tasks(herdb_ctx* ctx, const std::vector<const TaskReq*>& ts) {      // one task, or a coalesced group of map tasks
+    const TaskReq& t = *ts[0];
     u32 n = 0;
     int rc = pin_session_key(ctx, t.session, t.schema_type, &n);
     if (rc) return rc;
-    rc = t.reduce ? run_reduce_task(ctx, t, n) : run_map_task(ctx, t, n);
+    rc = t.reduce ? run_reduce_task(ctx, t, n) : run_map_tasks(ctx, ts, n);
     unpin_session_key(ctx, t.session);
     return rc;
+}
+
+bool same_circuit(const OwnedCircuit& a, const OwnedCircuit& b) {
+    return a.nodes.size() == b.nodes.size() && a.edges.size() == b.edges.size() && a.in_types == b.in_types && a.out_types == b.out_types &&
+           a.in_offs == b.in_offs && (a.nodes.empty() || !memcmp(a.nodes.data(), b.nodes.data(), a.nodes.size() * sizeof(herdb_node))) &&
+           (a.edges.empty() || !memcmp(a.edges.data(), b.edges.data(), a.edges.size() * sizeof(herdb_edge)));
 }
 
 }  // namespace
@@ -1348,31 +1392,65 @@ extern "C" uint64_t herdb_partition_rows(uint64_t rows, uint32_t partitions, uin
     return rows / partitions + (k < rows % partitions ? 1 : 0);
 }
 
+// Task threads.  A small map task is coalesced with the map tasks queued right behind it that belong to the same session
+// and carry the same circuit, up to HERDB_COALESCE_ROWS rows in total: herdsman cuts a frame into partitions
+// (storage_service.cpp:121-129) and a partition of a few hundred rows leaves most of a grid round empty at every level.
+// The group is evaluated as one batch (run_map_tasks); every task keeps its own files, handle and status.  If the group
+// fails, its tasks are run again one by one, so that only the task at fault reports the failure.
 static void worker_loop(herdb_ctx* ctx) {
     for (;;) {
-        TaskReq t;
+        std::vector<TaskReq> group;
         {
             std::unique_lock<std::mutex> l(ctx->q_mu);
-            ctx->q_cv.wait(l, [&] { return ctx->stop || !ctx->queue.empty(); });
+            // (while another thread is collecting a group, the tasks that arrive are its to look at first)
+            ctx->q_cv.wait(l, [&] { return ctx->stop || (!ctx->queue.empty() && !ctx->lingering); });
             if (ctx->queue.empty()) return;            // stop requested and nothing left
-            t = std::move(ctx->queue.front());
+            group.push_back(std::move(ctx->queue.front()));
             ctx->queue.pop_front();
             ctx->in_flight++;
+            if (!group[0].reduce && group[0].row_count < ctx->coalesce_rows) {
+                uint64_t total = group[0].row_count;
+                // wait up to 1 ms for the next task after every arrival, 5 ms in all (a task of a few hundred rows takes ~100 ms)
+                const auto t_first = std::chrono::steady_clock::now();
+                auto deadline = t_first + std::chrono::milliseconds(1);
+                ctx->lingering++;
+                for (;;) {
+                    if (ctx->queue.empty()) {          // the executor hands its window over task by task: linger for a moment
+                        if (ctx->stop || !ctx->q_cv.wait_until(l, deadline, [&] { return ctx->stop || !ctx->queue.empty(); }) || ctx->queue.empty()) break;
+                    }
+                    const TaskReq& nx = ctx->queue.front();
+                    if (nx.reduce || nx.session != group[0].session || nx.schema_type != group[0].schema_type ||
+                        total + nx.row_count > ctx->coalesce_rows || !same_circuit(nx.circuit, group[0].circuit)) break;
+                    total += nx.row_count;
+                    group.push_back(std::move(ctx->queue.front()));
+                    ctx->queue.pop_front();
+                    ctx->in_flight++;
+                    deadline = std::min(std::chrono::steady_clock::now() + std::chrono::milliseconds(1), t_first + std::chrono::milliseconds(5));
+                }
+                ctx->lingering--;
+            }
         }
-        const int rc = run_task(ctx, t);
-        // CUDA / IO / format errors => ERROR (job fails, executor.cpp:168-178).  Out of device or pinned memory is
-        // worth a retry (TIME_OUT => rescheduled up to three times, executor.cpp:136-167): the budgets that size a
-        // task's row chunks are halved first, so the retry runs with smaller buffers.
-        int status = rc == HERDB_OK ? HERDB_TASK_COMPLETED : HERDB_TASK_ERROR;
-        if (rc == HERDB_ERR_NOMEM) {
-            ctx->mem_budget = std::max<size_t>(ctx->mem_budget / 2, (size_t)64 << 20);
-            ctx->io_budget = std::max<size_t>(ctx->io_budget / 2, (size_t)16 << 20);
-            status = HERDB_TASK_TIME_OUT;
+        ctx->q_cv.notify_all();                        // what this thread left in the queue is for the others
+        std::vector<const TaskReq*> ptrs;
+        for (const TaskReq& t : group) ptrs.push_back(&t);
+        std::vector<int> rcs(group.size(), run_tasks(ctx, ptrs));
+        if (group.size() > 1 && rcs[0] != HERDB_OK)
+            for (size_t k = 0; k < group.size(); ++k) rcs[k] = run_tasks(ctx, std::vector<const TaskReq*>{&group[k]});
+        for (size_t k = 0; k < group.size(); ++k) {
+            // CUDA / IO / format errors => ERROR (job fails, executor.cpp:168-178).  Out of device or pinned memory is
+            // worth a retry (TIME_OUT => rescheduled up to three times, executor.cpp:136-167): the budgets that size a
+            // task's row chunks are halved first, so the retry runs with smaller buffers.
+            int status = rcs[k] == HERDB_OK ? HERDB_TASK_COMPLETED : HERDB_TASK_ERROR;
+            if (rcs[k] == HERDB_ERR_NOMEM) {
+                ctx->mem_budget = std::max<size_t>(ctx->mem_budget / 2, (size_t)64 << 20);
+                ctx->io_budget = std::max<size_t>(ctx->io_budget / 2, (size_t)16 << 20);
+                status = HERDB_TASK_TIME_OUT;
+            }
+            if (group[k].done) group[k].done(group[k].user, status);
         }
-        if (t.done) t.done(t.user, status);
         {
             std::lock_guard<std::mutex> l(ctx->q_mu);
-            ctx->in_flight--;
+            ctx->in_flight -= group.size();
         }
         ctx->idle_cv.notify_all();
     }

@@ -122,6 +122,8 @@ struct herdb_ctx {
     size_t mem_budget = 0;       // bytes of scratch per device for slots + ext
     size_t io_budget = 0;        // bytes per staging buffer of a lane (rows are chunked to fit)
     size_t key_budget = 0;       // bytes of key material per device before file-backed keys are evicted (LRU)
+    uint64_t coalesce_rows = 0;  // queued map tasks of one session with one circuit are evaluated together up to this many rows
+    int task_window = 1;         // tasks an IWorkerGroup on this context should keep outstanding (concurrent_workers())
     // keys
     std::mutex key_mu;
     std::map<std::string, herdb::KeyInfo> key_info;
@@ -133,6 +135,7 @@ struct herdb_ctx {
     std::condition_variable q_cv, idle_cv;
     std::deque<herdb::TaskReq> queue;
     size_t in_flight = 0;
+    int lingering = 0;           // task threads collecting a group of small tasks right now (worker_loop)
     bool stop = false;
     std::vector<std::thread> workers;
 

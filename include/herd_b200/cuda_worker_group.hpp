@@ -70,7 +70,7 @@ public:
 		{
 			throw std::runtime_error(std::string("CudaWorkerGroup: ") + herdb_strerror(rc));
 		}
-		concurrent_ = static_cast<std::size_t>(herdb_task_threads(ctx_));   // tasks the backend really runs at once
+		concurrent_ = static_cast<std::size_t>(herdb_task_window(ctx_));    // task threads + a queue small tasks are coalesced from
 		completer_ = std::thread([this]() { completer_body(); });
 	}
 

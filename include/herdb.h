@@ -115,6 +115,13 @@ int  herdb_device_count(const herdb_ctx* ctx);
 /* host threads that run tasks (default 2, HERDB_TASK_THREADS): what an IWorkerGroup built on this context
  * should answer to concurrent_workers() (i_worker_group.hpp:48; executor.cpp:96-113 keeps that many in flight) */
 int  herdb_task_threads(const herdb_ctx* ctx);
+/* tasks an IWorkerGroup built on this context should keep outstanding = its answer to concurrent_workers() (default 8,
+ * HERDB_TASK_WINDOW; never below the task threads).  Deeper than the task threads on purpose: small map tasks that wait
+ * in the queue behind one another -- same session, same circuit -- are coalesced into ONE evaluation of up to
+ * HERDB_COALESCE_ROWS rows (default 4096, 0 = off), because a partition of a few hundred rows fills only a fraction of a
+ * grid round per circuit level.  Every task keeps its own partition files, completion and status; if a coalesced
+ * evaluation fails, its tasks are re-run one by one so that only the task at fault fails. */
+int  herdb_task_window(const herdb_ctx* ctx);
 
 /* ------------------------------------------------------------------ keys
  * load_key reads <key_dir>/<session>/<schema_type>.key (key_service.cpp:28-31);

@@ -99,7 +99,7 @@ def test_two_tasks_in_flight_and_zero_output_columns(world):
     """concurrent_workers() == 2 == the backend's task threads: partitions scheduled back to back all complete, results
     are per-task correct"""
     w = world
-    assert w["wg"].concurrent_workers() == w["wg"].backend.task_threads() == 2
+    assert w["wg"].backend.task_threads() == 2 and w["wg"].concurrent_workers() == w["wg"].backend.task_window() == 8
     c = cm.adder_circuit(8)
     jobs = []
     for k in range(5):
@@ -112,6 +112,45 @@ def test_two_tasks_in_flight_and_zero_output_columns(world):
         assert h.wait(300) == api.TaskHandle.Status.COMPLETED
         got = api.partition_read(w["storage"] / w["session"] / out_df / "0", rows.shape[0], 8, w["n"])
         assert np.array_equal(got, w["oracle"].circuit_rows(c.to_c(), rows, 8))
+
+
+def test_small_map_tasks_are_coalesced_and_fail_individually(world):
+    """eight 6-row partitions of one frame scheduled at once (the executor's window is concurrent_workers() = 8): the task
+    threads evaluate them as one or two batches instead of eight (far fewer launches), every task still writes its own
+    partition, equal to the oracle's; a task whose partition is missing, queued in the middle of such a group, fails alone"""
+    w = world
+    be = w["wg"].backend
+    c = cm.adder_circuit(8)
+    levels = api.analyze(c)["levels"]
+    parts, per = 8, 6
+    x, y, rows = _adder_rows(w, parts * per, 123)
+    in_df, out_df = _new_df(w), _new_df(w)
+    for k in range(parts):
+        if k != 3:                                                  # partition 3 does not exist
+            api.partition_write(w["storage"] / w["session"] / in_df / str(k), rows[k * per:(k + 1) * per])
+    be.wait_idle(); be.reset_stats()
+    handles = [w["wg"].schedule_task(api.MapTask(w["session"], api.InputDataFramePtr(api.DataFramePtr(in_df, k), per),
+                                                 api.DataFramePtr(out_df, k), api.CryptoKeyPtr(1), c)) for k in range(parts)]
+    st = [h.wait(300) for h in handles]
+    assert [s == api.TaskHandle.Status.COMPLETED for s in st] == [k != 3 for k in range(parts)]
+    ref = w["oracle"].circuit_rows(c.to_c(), rows, 8)
+    for k in range(parts):
+        path = w["storage"] / w["session"] / out_df / str(k)
+        if k == 3:
+            assert not path.exists() and not path.with_name("3.tmp").exists()
+        else:
+            assert np.array_equal(api.partition_read(path, per, 8, w["n"]), ref[k * per:(k + 1) * per])
+    # uncoalesced: 7 tasks x `levels` blind-rotation launches; a failed group is re-run task by task (the fallback), so
+    # only a run without the bad task shows the saving
+    be.wait_idle(); be.reset_stats()
+    out2 = _new_df(w)
+    api.partition_write(w["storage"] / w["session"] / in_df / "3", rows[3 * per:4 * per])
+    handles = [w["wg"].schedule_task(api.MapTask(w["session"], api.InputDataFramePtr(api.DataFramePtr(in_df, k), per),
+                                                 api.DataFramePtr(out2, k), api.CryptoKeyPtr(1), c)) for k in range(parts)]
+    assert all(h.wait(300) == api.TaskHandle.Status.COMPLETED for h in handles)
+    got = np.concatenate([api.partition_read(w["storage"] / w["session"] / out2 / str(k), per, 8, w["n"]) for k in range(parts)])
+    assert np.array_equal(got, ref)
+    assert be.stats()["blind_rotate_launches"] <= parts * levels // 2, "tasks were not coalesced"
 
 
 @pytest.mark.parametrize("policy,parts,per_node", [("SEQUENCED", 3, 2), ("PARALLEL", 3, 2), ("PARALLEL_FULL", 5, 2), ("PARALLEL_FULL", 7, 3)])

@@ -206,7 +206,7 @@ def run(args, root):
     same = bool(np.array_equal(host, got))
     in_bytes = sum(c.in_bits for c in stages) * (N + 1) * 2 * R; out_bytes = sum(c.out_bits for c in stages) * (N + 1) * 2 * R
     line = {"config": args.config, "rows": R, "partitions": P, "devices": args.devices, "stages": len(stages), "gates_per_row": gates_per_row,
-            "task_threads": window, "dir": root,
+            "task_threads": be.task_threads(), "task_window": window, "dir": root,
             "seam": {"seconds": t_seam, "rows_per_s": R / t_seam, "gates_per_s": R * gates_per_row / t_seam,
                      "file_bytes_read": in_bytes, "file_bytes_written": out_bytes,
                      "kernel_ms_per_device": [s["blind_rotate_ms"] + s["keyswitch_ms"] for s in st]},
