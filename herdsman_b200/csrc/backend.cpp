@@ -639,11 +639,14 @@ int eval_rows_pipelined(herdb_ctx* ctx, const char* session, const EvalPlan& pla
     return HERDB_OK;
 }
 
-int session_n(herdb_ctx* ctx, const char* session, u32* n) {
+// the session's key as it is resident (no file check: that is the task seam's business), pinned against eviction and
+// unloading for the duration of the evaluation; pair with unpin_session_key
+int session_n_pinned(herdb_ctx* ctx, const char* session, u32* n) {
     std::lock_guard<std::mutex> l(ctx->key_mu);
     auto it = ctx->key_info.find(session);
     if (it == ctx->key_info.end()) { ctx->set_error("no key for session"); return HERDB_ERR_NOKEY; }
     it->second.last_use = ++ctx->key_clock;
+    it->second.pins++;
     *n = it->second.n;
     return HERDB_OK;
 }
@@ -652,16 +655,21 @@ int eval_host_rows(herdb_ctx* ctx, const char* session, const herdb_circuit* con
                    const uint16_t* rows_in, uint16_t* rows_out, size_t n_rows) {
     u32 n = 0;
     EvalPlan plan;
-    int rc = session_n(ctx, session, &n);
+    int rc = session_n_pinned(ctx, session, &n);
     if (rc == HERDB_ERR_NOKEY) {                     // the circuit is still validated (malformed circuits are refused without a key)
         rc = make_plan(ctx, circuits, n_stages, 0, kLweMax, plan);
         return rc ? rc : HERDB_ERR_NOKEY;
     }
-    rc = make_plan(ctx, circuits, n_stages, n_rows, n, plan); if (rc) return rc;
-    if (!n_rows) return HERDB_OK;
-    if ((!rows_in && plan.stages.front().in_bits) || (!rows_out && plan.stages.back().out_bits)) return HERDB_ERR_ARG;
-    RowIo io; io.src_mem = (const uint8_t*)rows_in; io.dst_mem = (uint8_t*)rows_out;
-    return eval_rows_pipelined(ctx, session, plan, io, n_rows);
+    rc = make_plan(ctx, circuits, n_stages, n_rows, n, plan);
+    if (!rc && n_rows) {
+        if ((!rows_in && plan.stages.front().in_bits) || (!rows_out && plan.stages.back().out_bits)) rc = HERDB_ERR_ARG;
+        else {
+            RowIo io; io.src_mem = (const uint8_t*)rows_in; io.dst_mem = (uint8_t*)rows_out;
+            rc = eval_rows_pipelined(ctx, session, plan, io, n_rows);
+        }
+    }
+    unpin_session_key(ctx, session);
+    return rc;
 }
 
 }  // namespace

@@ -91,6 +91,8 @@ def test_chunked_task_pipeline_matches_oracle(tmp_path, test_key, oracle_lib):
         assert np.array_equal(pin_out.numpy(), ref)
         piped = w["wg"].backend.eval_pipeline_rows(w["session"], cm.pipeline_stages(8), np.concatenate([rows, rows[:, :8]], axis=1))
         assert piped.shape == (70, 8, w["n"] + 1)
+        w["wg"].backend.unload_key(w["session"])          # evaluations pin the key only while they run
+        assert w["wg"].backend.loaded_keys() == 0
     finally:
         w["wg"].close()
 
